@@ -1,0 +1,377 @@
+// Device-side rigid-body transition of the bouncing-object model (float32, one body per thread).
+//
+// Replaces, for one particle: PhySMC.step = sync! ; forward_step  (PhySMC/PhySMC.jl:32-35,
+// PhySMC/PhyBullet/PhyBullet.jl:68-103, Elements/rigid_body.jl:33-76,129-139) and the Bullet
+// stepSimulation() it drives, for the scene of Model/bouncing_object.jl:24-86.
+// The scene is compile-time constant data; the body state lives in registers.  The contact path (narrow
+// phase + projected Gauss-Seidel rows) is out of line and only entered by threads that are near a static.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace smcphys {
+
+enum { SHAPE_SPHERE = 0, SHAPE_CUBE = 1 };
+
+struct f3 { float x, y, z; };
+__device__ __forceinline__ f3 mk3(float x, float y, float z) { f3 r; r.x = x; r.y = y; r.z = z; return r; }
+__device__ __forceinline__ f3 operator+(f3 a, f3 b) { return mk3(a.x + b.x, a.y + b.y, a.z + b.z); }
+__device__ __forceinline__ f3 operator-(f3 a, f3 b) { return mk3(a.x - b.x, a.y - b.y, a.z - b.z); }
+__device__ __forceinline__ f3 operator*(f3 a, float s) { return mk3(a.x * s, a.y * s, a.z * s); }
+__device__ __forceinline__ float dot3(f3 a, f3 b) { return a.x * b.x + a.y * b.y + a.z * b.z; }
+__device__ __forceinline__ f3 cross3(f3 a, f3 b) {
+  return mk3(a.y * b.z - a.z * b.y, a.z * b.x - a.x * b.z, a.x * b.y - a.y * b.x);
+}
+__device__ __forceinline__ float comp3(f3 a, int i) { return i == 0 ? a.x : (i == 1 ? a.y : a.z); }
+__device__ __forceinline__ void setc3(f3& a, int i, float v) {
+  if (i == 0) a.x = v; else if (i == 1) a.y = v; else a.z = v;
+}
+struct f4 { float x, y, z, w; };  // quaternion xyzw (rigid_body.jl:21)
+
+struct Body {
+  f3 x;  // position
+  f4 q;  // orientation
+  f3 v;  // linear velocity
+  f3 w;  // angular velocity, world frame
+};
+
+// ---- scene constants (Model/bouncing_object.jl:24-60) and Bullet solver constants
+#define PH_DT (1.0f / 240.0f)             // pb_timestep, PhyBullet.jl:27
+#define PH_H 0.05f                        // sphere radius / cube half extent, bouncing_object.jl:68,71
+#define PH_G (-9.81f)                     // bouncing_object.jl:58
+#define PH_STATIC_REST 0.5f               // restitution of every static, bouncing_object.jl:29-55
+#define PH_FRICTION 0.25f                 // lateralFriction 0.5 (body) x 0.5 (static)
+#define PH_DAMP 0.04f                     // btMultiBody linear = angular damping
+#define PH_ERP 0.08f                      // erp2
+#define PH_SLOP 1e-5f                     // linearSlop
+#define PH_REST_THRESH 0.2f               // restitutionVelocityThreshold
+#define PH_RESID 1e-7f                    // leastSquaresResidualThreshold
+#define PH_ITERS 50                       // numIterations
+#define PH_BOX_MARGIN 0.001f              // collision margin of a 0.01-thin btBoxShape
+#define PH_ANG_THRESH 0.78539816339744830962f
+#define PH_THR (0.02f * 1.7320508075688772f * PH_H)  // contact breaking threshold (0.02 x AABB radius)
+#define PH_MAXC 8
+#define PH_INV_M 1.0f                                // mass 1 (bouncing_object.jl:63)
+#define PH_INV_I_SPHERE (1.0f / (0.4f * PH_H * PH_H))          // 2/5 m r^2
+#define PH_INV_I_CUBE (6.0f / ((2.0f * PH_H) * (2.0f * PH_H)))  // m (2h)^2 / 6
+
+struct ScenePar {
+  float ceil_half;  // 0.01 (bouncing_object.jl:53); Tests/generate_trajectories.jl:52 uses 0.02
+};
+
+// the five static boxes in creation order (bouncing_object.jl:34-55)
+__device__ __forceinline__ void static_box(int b, float ceil_half, f3& c, f3& h) {
+  switch (b) {
+    case 0: c = mk3(-0.51f, 0.f, 0.51f); h = mk3(0.01f, 0.5f, 0.5f); break;
+    case 1: c = mk3(0.f, 0.51f, 0.51f); h = mk3(0.5f, 0.01f, 0.5f); break;
+    case 2: c = mk3(0.51f, 0.f, 0.51f); h = mk3(0.01f, 0.5f, 0.5f); break;
+    case 3: c = mk3(0.f, -0.51f, 0.51f); h = mk3(0.5f, 0.01f, 0.5f); break;
+    default: c = mk3(0.f, 0.f, 1.01f); h = mk3(0.5f, 0.5f, ceil_half); break;
+  }
+}
+
+struct Contact {
+  f3 r;  // arm: contact point on the body minus centre
+  f3 n;  // normal, static -> body
+  float dist;
+};
+
+// persistent plane manifold of the cube, reset at every macro step (sync! re-poses the body)
+struct Manifold {
+  int n;
+  f3 la[4];  // body-local corner
+  f3 wb[4];  // world point on the plane
+};
+
+__device__ __forceinline__ void rotmat(const f4& q, float R[3][3]) {
+  float d = q.x * q.x + q.y * q.y + q.z * q.z + q.w * q.w;
+  float s = 2.0f / d;
+  float xs = q.x * s, ys = q.y * s, zs = q.z * s;
+  float wx = q.w * xs, wy = q.w * ys, wz = q.w * zs;
+  float xx = q.x * xs, xy = q.x * ys, xz = q.x * zs;
+  float yy = q.y * ys, yz = q.y * zs, zz = q.z * zs;
+  R[0][0] = 1.0f - (yy + zz); R[0][1] = xy - wz; R[0][2] = xz + wy;
+  R[1][0] = xy + wz; R[1][1] = 1.0f - (xx + zz); R[1][2] = yz - wx;
+  R[2][0] = xz - wy; R[2][1] = yz + wx; R[2][2] = 1.0f - (xx + yy);
+}
+__device__ __forceinline__ f3 rotv(const float R[3][3], f3 v) {
+  return mk3(R[0][0] * v.x + R[0][1] * v.y + R[0][2] * v.z, R[1][0] * v.x + R[1][1] * v.y + R[1][2] * v.z,
+             R[2][0] * v.x + R[2][1] * v.y + R[2][2] * v.z);
+}
+
+// A body whose centre is inside this region touches nothing (every static is farther than the bounding
+// radius + margin + breaking threshold), so the narrow phase and the solver are skipped and a cube's
+// manifold empties (all of its cached points are beyond the breaking threshold).
+template <int SHAPE>
+__device__ __forceinline__ bool body_clear(const f3& x, float ceil_half) {
+  const float rad = (SHAPE == SHAPE_SPHERE) ? PH_H : 1.7320508075688772f * PH_H;
+  const float pad = rad + 2.0f * PH_THR;
+  return fabsf(x.x) < 0.5f - pad && fabsf(x.y) < 0.5f - pad && x.z > pad && x.z < 1.01f - ceil_half - pad;
+}
+
+// ---------------------------------------------------------------- narrow phase
+// sphere: plane (support point) then the five boxes (closest point on the margin-shrunk core; centre inside
+// the core -> minimum-translation face of the full box).
+__device__ __forceinline__ int collide_sphere(const ScenePar& sp, const Body& s, Contact* out) {
+  int nc = 0;
+  float d = s.x.z - PH_H;
+  if (d < PH_THR) { out[nc].r = mk3(0.f, 0.f, -PH_H); out[nc].n = mk3(0.f, 0.f, 1.f); out[nc].dist = d; nc++; }
+#pragma unroll
+  for (int b = 0; b < 5; b++) {
+    f3 c, h;
+    static_box(b, sp.ceil_half, c, h);
+    f3 cb = s.x - c;
+    f3 hc = mk3(h.x - PH_BOX_MARGIN, h.y - PH_BOX_MARGIN, h.z - PH_BOX_MARGIN);
+    f3 p = mk3(fminf(fmaxf(cb.x, -hc.x), hc.x), fminf(fmaxf(cb.y, -hc.y), hc.y), fminf(fmaxf(cb.z, -hc.z), hc.z));
+    f3 df = cb - p;
+    float d2 = dot3(df, df);
+    f3 n;
+    float dist;
+    if (d2 > 0.f) {
+      float dl = sqrtf(d2);
+      n = df * (1.0f / dl);
+      dist = dl - PH_H - PH_BOX_MARGIN;
+    } else {
+      int ax = 0;
+      float best = h.x - fabsf(cb.x);
+      float dy = h.y - fabsf(cb.y), dz = h.z - fabsf(cb.z);
+      if (dy < best) { best = dy; ax = 1; }
+      if (dz < best) { best = dz; ax = 2; }
+      n = mk3(0.f, 0.f, 0.f);
+      setc3(n, ax, comp3(cb, ax) >= 0.f ? 1.f : -1.f);
+      dist = -(best + PH_H);
+    }
+    if (dist < PH_THR && nc < PH_MAXC) { out[nc].r = n * (-PH_H); out[nc].n = n; out[nc].dist = dist; nc++; }
+  }
+  return nc;
+}
+
+// cube: one deepest support vertex per substep into the persistent plane manifold (keyed on the body-local
+// corner, refreshed and pruned every substep), then face-vertex contacts against the five boxes along the
+// axis of least overlap (the documented modelling choice of the oracle; Bullet's btBoxBoxDetector is not
+// restated anywhere in the reference tree).
+__device__ __forceinline__ int collide_cube(const ScenePar& sp, const Body& s, Manifold& pm, Contact* out) {
+  const float h = PH_H, thr = PH_THR;
+  int nc = 0;
+  float R[3][3];
+  rotmat(s.q, R);
+  {
+    f3 vl = mk3((-R[2][0]) >= 0.f ? h : -h, (-R[2][1]) >= 0.f ? h : -h, (-R[2][2]) >= 0.f ? h : -h);
+    f3 vw = s.x + rotv(R, vl);
+    float d = vw.z;
+    if (d < thr) {
+      int best = -1;
+      float sd = thr * thr;
+      for (int i = 0; i < pm.n; i++) {
+        f3 dd = pm.la[i] - vl;
+        float l2 = dot3(dd, dd);
+        if (l2 < sd) { sd = l2; best = i; }
+      }
+      f3 wb = mk3(vw.x, vw.y, 0.f);
+      if (best >= 0) { pm.la[best] = vl; pm.wb[best] = wb; }
+      else if (pm.n < 4) { pm.la[pm.n] = vl; pm.wb[pm.n] = wb; pm.n++; }
+    }
+    float dist[4];
+    f3 wa[4];
+    for (int i = pm.n - 1; i >= 0; i--) {
+      wa[i] = s.x + rotv(R, pm.la[i]);
+      dist[i] = wa[i].z - pm.wb[i].z;
+    }
+    for (int i = pm.n - 1; i >= 0; i--) {
+      bool drop = false;
+      if (dist[i] > thr) drop = true;
+      else {
+        float dx = pm.wb[i].x - wa[i].x, dy = pm.wb[i].y - wa[i].y;
+        if (dx * dx + dy * dy > thr * thr) drop = true;
+      }
+      if (drop) {
+        int last = pm.n - 1;
+        if (i != last) { pm.la[i] = pm.la[last]; pm.wb[i] = pm.wb[last]; wa[i] = wa[last]; dist[i] = dist[last]; }
+        pm.n--;
+      }
+    }
+    for (int i = 0; i < pm.n; i++) { out[nc].r = wa[i] - s.x; out[nc].n = mk3(0.f, 0.f, 1.f); out[nc].dist = dist[i]; nc++; }
+  }
+  for (int b = 0; b < 5; b++) {
+    f3 c, bh;
+    static_box(b, sp.ceil_half, c, bh);
+    f3 d = s.x - c;
+    float ex[3];
+#pragma unroll
+    for (int i = 0; i < 3; i++) ex[i] = h * (fabsf(R[i][0]) + fabsf(R[i][1]) + fabsf(R[i][2]));
+    float ov[3] = {bh.x + ex[0] - fabsf(d.x), bh.y + ex[1] - fabsf(d.y), bh.z + ex[2] - fabsf(d.z)};
+    if (ov[0] <= 0.f || ov[1] <= 0.f || ov[2] <= 0.f) continue;
+    int ax = 0;
+    if (ov[1] < ov[ax]) ax = 1;
+    if (ov[2] < ov[ax]) ax = 2;
+    float sgn = comp3(d, ax) >= 0.f ? 1.f : -1.f;
+    f3 n = mk3(0.f, 0.f, 0.f);
+    setc3(n, ax, sgn);
+    float face = comp3(c, ax) + sgn * comp3(bh, ax);
+    int j = 0;
+    if (fabsf(R[ax][1]) > fabsf(R[ax][j])) j = 1;
+    if (fabsf(R[ax][2]) > fabsf(R[ax][j])) j = 2;
+    float js = (R[ax][j] * sgn > 0.f) ? -1.f : 1.f;
+    int j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    int a1 = (ax + 1) % 3, a2 = (ax + 2) % 3;
+    for (int k = 0; k < 4; k++) {
+      f3 vl = mk3(0.f, 0.f, 0.f);
+      setc3(vl, j, js * h);
+      setc3(vl, j1, (k & 1) ? h : -h);
+      setc3(vl, j2, (k & 2) ? h : -h);
+      f3 rw = rotv(R, vl);
+      f3 vw = s.x + rw;
+      float gap = sgn * (comp3(vw, ax) - face);
+      if (gap > 0.f) continue;
+      if (fabsf(comp3(vw, a1) - comp3(c, a1)) > comp3(bh, a1)) continue;
+      if (fabsf(comp3(vw, a2) - comp3(c, a2)) > comp3(bh, a2)) continue;
+      if (nc < PH_MAXC) { out[nc].r = rw; out[nc].n = n; out[nc].dist = gap; nc++; }
+    }
+  }
+  return nc;
+}
+
+// btPlaneSpace1
+__device__ __forceinline__ void plane_space(f3 n, f3& p, f3& q) {
+  if (fabsf(n.z) > 0.70710678118654752440f) {
+    float a = n.y * n.y + n.z * n.z;
+    float k = 1.0f / sqrtf(a);
+    p = mk3(0.f, -n.z * k, n.y * k);
+    q = mk3(a * k, -n.x * p.z, n.x * p.y);
+  } else {
+    float a = n.x * n.x + n.y * n.y;
+    float k = 1.0f / sqrtf(a);
+    p = mk3(-n.y * k, n.x * k, 0.f);
+    q = mk3(-n.z * p.y, n.z * p.x, a * k);
+  }
+}
+
+// ---------------------------------------------------------------- contact rows + projected Gauss-Seidel
+// One normal row and two friction rows (implicit cone, mu = 0.25) per contact; <= 50 sweeps, normal rows
+// first, early exit when the largest squared velocity change of a sweep is <= 1e-7; no warm starting.
+// Restitution e_body * 0.5 applies only when |v_n| >= 0.2; penetration is recovered at erp 0.08.
+template <int SHAPE>
+__device__ __forceinline__ void solve_contacts(const Contact* c, int nc, float restitution, f3& v, f3& w) {
+  const float inv_m = PH_INV_M;
+  const float inv_i = (SHAPE == SHAPE_SPHERE) ? PH_INV_I_SPHERE : PH_INV_I_CUBE;
+  const float crest = restitution * PH_STATIC_REST;
+  f3 dir[PH_MAXC][3], rxn[PH_MAXC][3];
+  float dinv[PH_MAXC][3], rhs[PH_MAXC][3], app[PH_MAXC][3];
+  for (int i = 0; i < nc; i++) {
+    dir[i][0] = c[i].n;
+    plane_space(c[i].n, dir[i][1], dir[i][2]);
+    float relv[3];
+#pragma unroll
+    for (int k = 0; k < 3; k++) {
+      rxn[i][k] = cross3(c[i].r, dir[i][k]);
+      dinv[i][k] = 1.0f / (inv_m + dot3(rxn[i][k], rxn[i][k]) * inv_i);
+      relv[k] = dot3(dir[i][k], v) + dot3(rxn[i][k], w);
+      app[i][k] = 0.f;
+    }
+    float rest = 0.f;
+    if (fabsf(relv[0]) >= PH_REST_THRESH) rest = fmaxf(0.f, -crest * relv[0]);
+    float distance = c[i].dist + PH_SLOP;
+    float verr = rest - relv[0], perr = 0.f;
+    if (distance > 0.f) verr -= distance / PH_DT;
+    else perr = -distance * PH_ERP / PH_DT;
+    rhs[i][0] = (perr + verr) * dinv[i][0];
+    rhs[i][1] = -relv[1] * dinv[i][1];
+    rhs[i][2] = -relv[2] * dinv[i][2];
+  }
+  f3 dv = mk3(0.f, 0.f, 0.f), dw = mk3(0.f, 0.f, 0.f);
+  for (int it = 0; it < PH_ITERS; it++) {
+    float resid = 0.f;
+    for (int i = 0; i < nc; i++) {
+      float dimp = rhs[i][0] - (dot3(dir[i][0], dv) + dot3(rxn[i][0], dw)) * dinv[i][0];
+      float sum = app[i][0] + dimp;
+      if (sum < 0.f) { dimp = -app[i][0]; app[i][0] = 0.f; }
+      else app[i][0] = sum;
+      dv = dv + dir[i][0] * (dimp * inv_m);
+      dw = dw + rxn[i][0] * (dimp * inv_i);
+      float dvel = dimp / dinv[i][0];
+      resid = fmaxf(resid, dvel * dvel);
+    }
+    for (int i = 0; i < nc; i++) {
+      float lim = PH_FRICTION * app[i][0];
+      float sm[2];
+#pragma unroll
+      for (int k = 1; k <= 2; k++) {
+        float dimp = rhs[i][k] - (dot3(dir[i][k], dv) + dot3(rxn[i][k], dw)) * dinv[i][k];
+        sm[k - 1] = app[i][k] + dimp;
+      }
+      float l2 = sm[0] * sm[0] + sm[1] * sm[1];
+      if (l2 > lim * lim) {
+        float scl = lim / sqrtf(l2);
+        sm[0] *= scl;
+        sm[1] *= scl;
+      }
+#pragma unroll
+      for (int k = 1; k <= 2; k++) {
+        float dimp = sm[k - 1] - app[i][k];
+        app[i][k] = sm[k - 1];
+        dv = dv + dir[i][k] * (dimp * inv_m);
+        dw = dw + rxn[i][k] * (dimp * inv_i);
+        float dvel = dimp / dinv[i][k];
+        resid = fmaxf(resid, dvel * dvel);
+      }
+    }
+    if (resid <= PH_RESID) break;
+  }
+  v = v + dv;
+  w = w + dw;
+}
+
+// ---------------------------------------------------------------- one 1/240 s substep (Bullet stepSimulation)
+// Order (pinned by the reference's PyBullet cube fixture, see oracle/smc_oracle.hpp): narrow phase at the
+// current pose; v += dt (g - k v (1 + |v|)), same drag on omega; contact solve; x += dt v; q <- exp(w dt/2) q.
+// TRACK_Q = false drops the orientation update: a sphere's orientation never feeds back into its motion,
+// so the particle-filter kernels do not carry it (PhySMC.forward_step on a batch does).
+template <int SHAPE, bool TRACK_Q>
+__device__ __forceinline__ void substep(const ScenePar& sp, float restitution, Body& s, Manifold& pm) {
+  const float dt = PH_DT;
+  Contact c[PH_MAXC];
+  int nc = 0;
+  const bool clear = body_clear<SHAPE>(s.x, sp.ceil_half);
+  if (!clear) {
+    if (SHAPE == SHAPE_SPHERE) nc = collide_sphere(sp, s, c);
+    else nc = collide_cube(sp, s, pm, c);
+  } else if (SHAPE == SHAPE_CUBE) {
+    pm.n = 0;
+  }
+  {
+    float vn = sqrtf(dot3(s.v, s.v));
+    float f = PH_DAMP * (1.0f + vn);
+    s.v = mk3(s.v.x + dt * (-f * s.v.x), s.v.y + dt * (-f * s.v.y), s.v.z + dt * (PH_G - f * s.v.z));
+    float wn = sqrtf(dot3(s.w, s.w));
+    float fw = PH_DAMP * (1.0f + wn);
+    s.w = mk3(s.w.x + dt * (-fw * s.w.x), s.w.y + dt * (-fw * s.w.y), s.w.z + dt * (-fw * s.w.z));
+  }
+  if (nc > 0) solve_contacts<SHAPE>(c, nc, restitution, s.v, s.w);
+  s.x = s.x + s.v * dt;
+  if (TRACK_Q || SHAPE == SHAPE_CUBE) {
+    float ang = sqrtf(dot3(s.w, s.w));
+    if (ang * dt > PH_ANG_THRESH) ang = 0.5f * 1.57079632679489661923f / dt;
+    f3 ax;
+    if (ang < 0.001f) ax = s.w * (0.5f * dt - (dt * dt * dt) * 0.020833333333f * ang * ang);
+    else ax = s.w * (sinf(0.5f * ang * dt) / ang);
+    float cw = cosf(ang * dt * 0.5f);
+    f4 q = s.q, r;
+    r.x = cw * q.x + ax.x * q.w + ax.y * q.z - ax.z * q.y;
+    r.y = cw * q.y - ax.x * q.z + ax.y * q.w + ax.z * q.x;
+    r.z = cw * q.z + ax.x * q.y - ax.y * q.x + ax.z * q.w;
+    r.w = cw * q.w - ax.x * q.x - ax.y * q.y - ax.z * q.z;
+    float inv = 1.0f / sqrtf(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w);
+    s.q.x = r.x * inv; s.q.y = r.y * inv; s.q.z = r.z * inv; s.q.w = r.w * inv;
+  }
+}
+
+// PhySMC.step = sync! ; forward_step (PhySMC.jl:32-35): the body is re-posed, so the contact cache starts
+// cold, then S substeps run (S = 5 at step_dur 1/60, 9 at 1/30: `while dt <= step_dur`, PhyBullet.jl:82-88).
+template <int SHAPE, bool TRACK_Q>
+__device__ __forceinline__ void macro_step(const ScenePar& sp, float restitution, int S, Body& s) {
+  Manifold pm;
+  pm.n = 0;
+  for (int k = 0; k < S; k++) substep<SHAPE, TRACK_Q>(sp, restitution, s, pm);
+}
+
+}  // namespace smcphys

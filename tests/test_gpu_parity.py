@@ -1,0 +1,232 @@
+"""GPU parity: the CUDA path (through the C ABI) against the CPU oracle on the same seeded inputs.
+
+Tolerances:
+  T0  free flight, one macro step, GPU f32 vs oracle f64           <= 2e-6 m
+  T1  full trajectories, identical (e, init, noise draws)         <= 1e-4 m sphere, <= 1e-3 m cube, on the particles
+      whose contact-branch decisions agree; the fraction that flips a decision is bounded and reported
+  T3  resampling indices and integer weight sums                   bit exact
+  T4  posterior mean / sd of the elasticity vs the oracle         within 3 Monte Carlo standard errors
+"""
+import numpy as np
+import pytest
+
+from oracle import oracle as orc
+
+pytestmark = pytest.mark.gpu
+
+INIT_POS, INIT_VEL = [0.1, -0.2, 0.6], [3.0, -2.0, 1.5]
+
+
+@pytest.fixture(scope="module")
+def sp():
+    import __graft_entry__ as entry
+    entry.build()
+    import smc_physics_b200 as m
+    return m
+
+
+def _truth_path(shape, e_gt, T, S=5):
+    mu = orc.macro_rollout(shape, e_gt, orc.state13(INIT_POS, vel=INIT_VEL), T, S=S)[:, 0:3]
+    return np.vstack([np.asarray(INIT_POS)[None], mu[:-1]])   # row 1 = initial position (RealFlow convention)
+
+
+def _random_states(rng, n, free=True):
+    st = np.zeros((n, 13), np.float32)
+    lo, hi = (0.2, 0.8) if free else (-0.55, 0.55)
+    st[:, 0:2] = rng.uniform(lo - 0.5 if free else lo, hi - 0.5 if free else hi, (n, 2))
+    st[:, 2] = rng.uniform(0.25, 0.75, n) if free else rng.uniform(-0.02, 1.05, n)
+    q = rng.standard_normal((n, 4))
+    st[:, 3:7] = q / np.linalg.norm(q, axis=1, keepdims=True)
+    st[:, 7:10] = rng.uniform(-0.5, 0.5, (n, 3)) if free else rng.uniform(-5, 5, (n, 3))
+    st[:, 10:13] = rng.uniform(-3, 3, (n, 3))
+    return st
+
+
+@pytest.mark.parametrize("shape", [0, 1])
+def test_T0_free_flight_macro_step(sp, shape):
+    rng = np.random.default_rng(1)
+    st = _random_states(rng, 512, free=True)
+    e = rng.uniform(0, 1, 512).astype(np.float32)
+    out = sp.sim_step(shape, st, e, S=5)
+    for i in range(0, 512, 7):
+        ref = orc.macro_rollout(shape, float(e[i]), st[i].astype(np.float64), 1, S=5)[0]
+        assert np.abs(out[i, 0:3] - ref[0:3]).max() < 2e-6
+        assert np.abs(out[i, 7:13] - ref[7:13]).max() < 2e-5
+        assert min(np.abs(out[i, 3:7] - ref[3:7]).max(), np.abs(out[i, 3:7] + ref[3:7]).max()) < 1e-5
+
+
+@pytest.mark.parametrize("shape,tol", [(0, 1e-4), (1, 1e-3)])
+def test_contact_macro_step_vs_f32_oracle(sp, shape, tol):
+    """Bodies thrown at the floor, walls, corners and ceiling (also from outside the arena): one PhySMC.step."""
+    rng = np.random.default_rng(2)
+    n = 2048
+    st = _random_states(rng, n, free=False)
+    e = rng.uniform(0, 1, n).astype(np.float32)
+    for S in (5, 9):
+        out = sp.sim_step(shape, st, e, S=S)
+        ref = np.stack([orc.macro_rollout(shape, float(e[i]), st[i].astype(np.float64), 1, S=S, f32=True)[0]
+                        for i in range(n)])
+        err = np.abs(out[:, 0:3] - ref[:, 0:3]).max(axis=1)
+        assert np.isfinite(out).all()
+        assert (err < tol).mean() > 0.97, (S, (err < tol).mean(), np.sort(err)[-5:])
+        assert np.median(err) < 1e-6
+
+
+@pytest.mark.parametrize("shape,S,tol", [(0, 5, 1e-4), (0, 9, 1e-4), (1, 5, 1e-3)])
+def test_T1_trajectories_identical_noise(sp, shape, S, tol):
+    rng = np.random.default_rng(10 + shape + S)
+    n, T = 1024, 120
+    path = _truth_path(shape, 0.6, T, S)
+    e = rng.uniform(0, 1, n).astype(np.float32)
+    xt = (path[:, :, None] + 0.03 * rng.standard_normal((T, 3, n))).astype(np.float32)
+    mu_g, lp_g, st_g = sp.simulate(shape, S, INIT_POS, INIT_VEL, e, xt)
+    mu_o, lp_o, st_o = orc.simulate(shape, S, INIT_POS, INIT_VEL, e, xt, f32=True, threads=8)
+    err = np.abs(mu_g.astype(np.float64) - mu_o).max(axis=(0, 1))
+    agree = err < tol
+    # a contact-branch flip (in / out of the breaking threshold, restitution threshold) sends the two float32
+    # evaluations down different branches; those particles are counted, not compared
+    assert agree.mean() > 0.90, (agree.mean(), np.sort(err)[-10:])
+    assert np.median(err) < 2e-5
+    # transition log density of the agreeing particles
+    rel = np.abs(lp_g[agree] - lp_o[agree]) / (1.0 + np.abs(lp_o[agree]))
+    assert rel.max() < 1e-2 and np.median(rel) < 1e-5
+    print("T1 shape=%d S=%d: agree %.4f, median err %.2e" % (shape, S, agree.mean(), np.median(err)))
+
+
+def test_simulate_edge_cases(sp):
+    # zero particles / zero steps are accepted and touch nothing
+    mu, lp, st = sp.simulate(0, 5, INIT_POS, INIT_VEL, np.zeros(0, np.float32), np.zeros((4, 3, 0), np.float32))
+    assert mu.shape == (4, 3, 0)
+    mu, lp, st = sp.simulate(0, 5, INIT_POS, INIT_VEL, np.full(3, 0.5, np.float32), np.zeros((0, 3, 3), np.float32))
+    assert np.allclose(st[:, 0:3], INIT_POS) and np.all(lp == 0)
+    # ragged size (not a multiple of the block) and a single particle
+    for n in (1, 129):
+        xt = np.tile(np.asarray(INIT_POS, np.float32)[None, :, None], (3, 1, n))
+        mu, lp, st = sp.simulate(0, 5, INIT_POS, INIT_VEL, np.full(n, 0.3, np.float32), xt)
+        mo, lo, so = orc.simulate(0, 5, INIT_POS, INIT_VEL, np.full(n, 0.3, np.float32), xt, f32=True)
+        assert np.abs(mu - mo).max() < 1e-5 and np.abs(lp - lo).max() < 1e-3
+
+
+# ------------------------------------------------------------------ resampling: bit exact
+@pytest.mark.parametrize("n", [1, 2, 3, 31, 32, 33, 1000, 1023, 1024, 1025, 4096, 100003, 1 << 20])
+def test_T3_resample_indices_bit_exact(sp, n):
+    rng = np.random.default_rng(n)
+    for spread in (0.1, 3.0, 30.0):
+        lw = rng.normal(0, spread, n) - 1234.5
+        for u0 in (0.0, float(rng.uniform()), 1.0 - 2.0**-32):
+            got = sp.resample_systematic(lw, u0)
+            want = orc.resample_systematic(lw, u0)
+            assert np.array_equal(got, want), (n, spread, u0, np.flatnonzero(got != want)[:5])
+
+
+def test_T3_resample_degenerate_weights(sp):
+    n = 5000
+    lw = np.full(n, -np.inf)
+    lw[1234] = -3.0                       # a single survivor
+    assert np.all(sp.resample_systematic(lw, 0.5) == 1234)
+    lw = np.zeros(n)                      # equal weights: identity
+    assert np.array_equal(sp.resample_systematic(lw, 0.25), np.arange(n))
+    lw = np.zeros(n)
+    lw[::2] = -800.0                      # underflow to zero weight: never chosen
+    idx = sp.resample_systematic(lw, 0.7)
+    assert np.all(idx % 2 == 1) and np.array_equal(idx, orc.resample_systematic(lw, 0.7))
+    assert np.all(np.diff(idx) >= 0)      # systematic resampling is order preserving
+
+
+def test_T3_weight_sums_exact_and_textbook_agreement(sp):
+    rng = np.random.default_rng(9)
+    for n in (17, 1024, 50000, 1 << 20):
+        lw = rng.normal(0, 5, n)
+        g, o = sp.weight_stats(lw), orc.weight_stats(lw)
+        assert (g["W"], g["S1"], g["S2"]) == (o["W"], o["S1"], o["S2"])
+        assert g["mx"] == o["mx"] and g["below_half"] == o["below_half"]
+        assert abs(g["ess"] - o["ess"]) <= 1e-12 * o["ess"] and abs(g["lse"] - o["lse"]) <= 1e-12
+        # float64 textbook definitions
+        w = np.exp(lw - lw.max())
+        assert abs(g["ess"] - w.sum() ** 2 / (w * w).sum()) < 2e-4 * g["ess"]
+        assert abs(g["lse"] - (lw.max() + np.log(w.sum()))) < 1e-9
+    # the integer CDF picks the same ancestors as the float64 cumulative sum (ties have measure zero)
+    lw = rng.normal(0, 2, 20000)
+    a, b = sp.resample_systematic(lw, 0.123), orc.resample_systematic(lw, 0.123, f64_textbook=True)
+    assert (a != b).mean() < 1e-3
+
+
+def test_full_size_resample_properties(sp):
+    """N = 2^24 (BASELINE config 5): properties that do not need the sequential oracle."""
+    n = 1 << 24
+    rng = np.random.default_rng(11)
+    lw = rng.normal(0, 2, n)
+    idx = sp.resample_systematic(lw, 0.5)
+    assert idx.min() >= 0 and idx.max() < n and np.all(np.diff(idx) >= 0)
+    counts = np.bincount(idx, minlength=n)
+    w = np.exp(lw - lw.max())
+    expect = n * w / w.sum()
+    assert np.abs(counts - expect).max() < 1.0 + 1e-6      # systematic: offspring = floor or ceil of N w_i
+    assert counts.sum() == n
+
+
+# ------------------------------------------------------------------ the filter
+def test_run_smc_small_matches_oracle_draw_for_draw(sp):
+    """Same Philox counters on both sides: with N = 64 and a short horizon the two runs make the same draws and
+    the same accept / resample decisions except where a float32 branch flips."""
+    T = 12
+    path = _truth_path(0, 0.6, T)
+    with sp.ParticleFilter(num_particles=64, shape=0, substeps=5, max_timesteps=T, seed=99) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        stats = pf.run_smc(R=2)
+        out = pf.get_particles(want_traj=True)
+        log_ml = pf.get_log_ml()
+    ref = orc.run_smc(0, 64, 2, 5, INIT_POS, INIT_VEL, path, seed=99, f32=True, want_traj=True)
+    assert [s["resampled"] for s in stats] == [bool(r) for r in ref["stats"][:, 3]]
+    assert np.allclose([s["ess"] for s in stats], ref["stats"][:, 0], rtol=1e-3)
+    assert np.allclose([s["accept_rate"] for s in stats], ref["stats"][:, 2], atol=2.0 / 128)
+    assert (np.abs(out["e"] - ref["e"]) < 1e-9).mean() > 0.9
+    assert np.allclose(np.sort(out["e"]), np.sort(ref["e"]), atol=0.05)
+    assert abs(log_ml - ref["log_ml"]) < 1e-2 * (1 + abs(ref["log_ml"]))
+    same = np.abs(out["e"] - ref["e"]) < 1e-9
+    assert np.abs(out["traj"][:, :, same] - ref["traj"][:, :, same]).max() < 1e-4
+
+
+@pytest.mark.parametrize("shape,R", [(0, 2), (1, 1)])
+def test_T4_posterior_within_mc_error(sp, shape, R):
+    T, N, seeds = 30, 256, 16
+    path = _truth_path(shape, 0.7, T)
+    g_mean, o_mean, g_sd, o_sd = [], [], [], []
+    for s in range(seeds):
+        with sp.ParticleFilter(num_particles=N, shape=shape, substeps=5, max_timesteps=T, seed=1000 + s) as pf:
+            pf.set_trial(INIT_POS, INIT_VEL, path)
+            pf.run_smc(R=R, want_stats=False)
+            e = pf.get_particles(want_score=False)["e"]
+        ref = orc.run_smc(shape, N, R, 5, INIT_POS, INIT_VEL, path, seed=5000 + s, f32=True, threads=8)["e"]
+        g_mean.append(e.mean()); o_mean.append(ref.mean()); g_sd.append(e.std()); o_sd.append(ref.std())
+    g_mean, o_mean, g_sd, o_sd = map(np.asarray, (g_mean, o_mean, g_sd, o_sd))
+    se = np.sqrt(g_mean.var(ddof=1) / seeds + o_mean.var(ddof=1) / seeds)
+    assert abs(g_mean.mean() - o_mean.mean()) < 3 * se + 1e-3, (g_mean.mean(), o_mean.mean(), se)
+    se_sd = np.sqrt(g_sd.var(ddof=1) / seeds + o_sd.var(ddof=1) / seeds)
+    assert abs(g_sd.mean() - o_sd.mean()) < 3 * se_sd + 1e-3, (g_sd.mean(), o_sd.mean(), se_sd)
+
+
+def test_score_and_states_are_consistent(sp):
+    T = 20
+    path = _truth_path(0, 0.5, T)
+    with sp.ParticleFilter(num_particles=200, shape=0, substeps=5, max_timesteps=T, seed=3) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        pf.run_smc(R=1, want_stats=False)
+        out = pf.get_particles(want_traj=True)
+        st = pf.get_states()
+    assert np.isfinite(out["score"]).all() and np.isfinite(st).all()
+    assert np.abs(st[:, 0:3] - out["traj"][-1].T).max() < 1e-6          # last simulator output = final state
+    assert np.abs(np.linalg.norm(st[:, 3:7], axis=1) - 1).max() < 1e-5
+
+
+def test_call_order_errors(sp):
+    with sp.ParticleFilter(num_particles=16, max_timesteps=8) as pf:
+        with pytest.raises(sp.SmcphysError) as ei:
+            pf.run_smc()
+        assert ei.value.code == -3
+        with pytest.raises(sp.SmcphysError):
+            pf.set_trial(INIT_POS, INIT_VEL, np.zeros((9, 3)))       # T > max_timesteps
+        pf.set_trial(INIT_POS, INIT_VEL, np.zeros((0, 3)))           # empty observation list: prior only
+        pf.run_smc()
+        e = pf.get_particles(want_score=False)["e"]
+        assert e.min() > 0 and e.max() < 1
