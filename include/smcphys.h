@@ -137,6 +137,16 @@ int smcphys_resample_systematic(int32_t device, const double* log_w, int64_t n, 
 /* out3 = {max, ESS, LSE}; sums3 = {W, S1, S2} */
 int smcphys_weight_stats(int32_t device, const double* log_w, int64_t n, double* out3, uint64_t* sums3);
 
+/* ---- per-kernel device timing (CUDA events on the handle's stream around each launch of a kernel class) */
+#define SMCPHYS_K_EXTEND 0     /* k_extend: noise draw + observation weight + PhySMC.step */
+#define SMCPHYS_K_WEIGHTS 1    /* k_weight_sums + k_cdf + k_index: LSE / ESS / integer CDF / systematic indices */
+#define SMCPHYS_K_GATHER 2     /* k_gather + k_gather_hist (or k_pack / k_unpack on a sharded filter) */
+#define SMCPHYS_K_REJUVENATE 3 /* k_rejuvenate: re-simulate + Metropolis-Hastings */
+#define SMCPHYS_K_CLASSES 4
+int smcphys_set_profiling(smcphys_handle* h, int32_t on);
+/* synchronises, then adds the elapsed time of every recorded launch group of `kclass` since the last call */
+int smcphys_kernel_time(smcphys_handle* h, int32_t kclass, double* ms_total, int64_t* groups);
+
 /* measured FP32 FMA throughput of the device in TFLOP/s: the roofline denominator of the simulate kernels */
 int smcphys_fp32_peak(int32_t device, double* tflops);
 

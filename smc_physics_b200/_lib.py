@@ -68,6 +68,8 @@ SIGNATURES = {
                                    C.c_int64, C.c_int32, _fp, _dp, _fp]),
     "smcphys_resample_systematic": (C.c_int, [C.c_int32, _dp, C.c_int64, C.c_double, _ip]),
     "smcphys_weight_stats": (C.c_int, [C.c_int32, _dp, C.c_int64, _dp, _up]),
+    "smcphys_set_profiling": (C.c_int, [_H, C.c_int32]),
+    "smcphys_kernel_time": (C.c_int, [_H, C.c_int32, _dp, _ip]),
     "smcphys_fp32_peak": (C.c_int, [C.c_int32, _dp]),
 }
 

@@ -131,6 +131,15 @@ class ParticleFilter:
         return [dict(ess=s.ess, lse=s.lse, accept_rate=s.accept_rate, resampled=bool(s.resampled))
                 for s in stats[:self.T]]
 
+    def set_profiling(self, on=True):
+        check(lib().smcphys_set_profiling(self._h, int(bool(on))))
+
+    def kernel_time(self, kclass):
+        """(total ms, launch groups) of kernel class `kclass` since the last query (synchronises)."""
+        ms, cnt = C.c_double(), C.c_int64()
+        check(lib().smcphys_kernel_time(self._h, kclass, C.byref(ms), C.byref(cnt)))
+        return ms.value, cnt.value
+
     def synchronize(self):
         check(lib().smcphys_synchronize(self._h))
 
@@ -186,6 +195,16 @@ class ParticleFilter:
 
     def pf_rejuvenate(self, t, R, d_accept=None):
         check(lib().smcphys_pf_rejuvenate(self._h, t, R, C.c_void_p(d_accept)))
+
+
+K_EXTEND, K_WEIGHTS, K_GATHER, K_REJUVENATE = 0, 1, 2, 3
+
+
+def fp32_peak(device=0):
+    """Measured FP32 FMA throughput (TFLOP/s) of the device: roofline denominator of the simulate kernels."""
+    v = C.c_double()
+    check(lib().smcphys_fp32_peak(device, C.byref(v)))
+    return v.value
 
 
 def offspring_range(W_before, W_local, W_total, N, u0):

@@ -650,6 +650,28 @@ struct smcphys_handle {
   int steps_done = -1;  // PF steps applied to the particles; -1 = not initialised
   int ntiles = 0;
   std::vector<void*> allocs;
+  bool prof = false;
+  struct Ev { int cls; cudaEvent_t a, b; };
+  std::vector<Ev> evs;
+  std::vector<cudaEvent_t> ev_pool;
+};
+
+// event pair around one launch group of a kernel class (only when profiling is on)
+struct ProfScope {
+  smcphys_handle* h;
+  cudaEvent_t b = nullptr;
+  ProfScope(smcphys_handle* h_, int cls) : h(h_) {
+    if (!h->prof) return;
+    cudaEvent_t a = nullptr;
+    auto take = [&](cudaEvent_t& e) {
+      if (!h->ev_pool.empty()) { e = h->ev_pool.back(); h->ev_pool.pop_back(); }
+      else cudaEventCreate(&e);
+    };
+    take(a); take(b);
+    cudaEventRecord(a, h->stream);
+    h->evs.push_back({cls, a, b});
+  }
+  ~ProfScope() { if (b) cudaEventRecord(b, h->stream); }
 };
 
 static inline unsigned int nblk(int64_t n, int b) { return (unsigned int)((n + b - 1) / b); }
@@ -753,6 +775,8 @@ int smcphys_destroy(smcphys_handle* h) {
   cudaSetDevice(h->cfg.device);
   if (h->stream) cudaStreamSynchronize(h->stream);
   for (void* p : h->allocs) cudaFree(p);
+  for (auto& e : h->evs) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+  for (auto e : h->ev_pool) cudaEventDestroy(e);
   if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
   delete h;
   return 0;
@@ -765,6 +789,35 @@ int smcphys_set_stream(smcphys_handle* h, void* cuda_stream) {
   if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
   h->own_stream = false;
   h->stream = (cudaStream_t)cuda_stream;
+  return 0;
+}
+
+int smcphys_set_profiling(smcphys_handle* h, int32_t on) {
+  if (!h) return fail(SMCPHYS_EINVAL, "NULL handle");
+  h->prof = on != 0;
+  return 0;
+}
+
+int smcphys_kernel_time(smcphys_handle* h, int32_t kclass, double* ms_total, int64_t* groups) {
+  if (!h || !ms_total) return fail(SMCPHYS_EINVAL, "NULL argument");
+  if (kclass < 0 || kclass >= SMCPHYS_K_CLASSES) return fail(SMCPHYS_EINVAL, "unknown kernel class");
+  CK(cudaSetDevice(h->cfg.device));
+  CK(cudaStreamSynchronize(h->stream));
+  double tot = 0;
+  int64_t cnt = 0;
+  std::vector<smcphys_handle::Ev> rest;
+  for (auto& e : h->evs) {
+    if (e.cls != kclass) { rest.push_back(e); continue; }
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, e.a, e.b));
+    tot += ms;
+    cnt++;
+    h->ev_pool.push_back(e.a);
+    h->ev_pool.push_back(e.b);
+  }
+  h->evs.swap(rest);
+  *ms_total = tot;
+  if (groups) *groups = cnt;
   return 0;
 }
 
@@ -816,6 +869,7 @@ int smcphys_pf_extend(smcphys_handle* h, int32_t t, double* d_local_max) {
   const int64_t n = h->cfg.num_particles;
   const double* y = &h->obs[(size_t)t * 3];
   LAUNCH(k_step_begin, 1, 1, h->stream, h->ctl);
+  ProfScope ps(h, SMCPHYS_K_EXTEND);
   if (h->cfg.shape == SMCPHYS_SPHERE)
     LAUNCH(k_extend<SHAPE_SPHERE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B, h->ctl, h->tp, h->sp, n,
            h->cfg.particle_offset, h->cfg.seed, t, h->cfg.substeps, y[0], y[1], y[2]);
@@ -830,6 +884,7 @@ int smcphys_pf_extend(smcphys_handle* h, int32_t t, double* d_local_max) {
 
 static int weight_sums(smcphys_handle* h, const double* d_gmax, int decide, int t, u64* d_sums) {
   const int64_t n = h->cfg.num_particles;
+  ProfScope ps(h, SMCPHYS_K_WEIGHTS);
   LAUNCH(k_weight_sums, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, d_gmax, n, h->ntiles, decide,
          h->cfg.ess_num, h->cfg.ess_den, t, h->d_ess, h->d_lse, h->d_res, d_sums);
   return 0;
@@ -852,8 +907,12 @@ int smcphys_pf_resample_local(smcphys_handle* h, int32_t t) {
   if (rc) return rc;
   uint32_t r[4];
   philox4x32_10(h->cfg.seed, 0u, (uint32_t)t, 0u, (uint32_t)ST_RESAMPLE, r);
-  LAUNCH(k_cdf, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, &h->ctl->gmax, n, (u64)0, 1);
-  LAUNCH(k_index, nblk(n, 256), 256, h->stream, h->B, h->ctl, n, n, (u64)r[0], &h->ctl->W, (u64)0, (int64_t)0, n, 1);
+  {
+    ProfScope ps(h, SMCPHYS_K_WEIGHTS);
+    LAUNCH(k_cdf, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, &h->ctl->gmax, n, (u64)0, 1);
+    LAUNCH(k_index, nblk(n, 256), 256, h->stream, h->B, h->ctl, n, n, (u64)r[0], &h->ctl->W, (u64)0, (int64_t)0, n, 1);
+  }
+  ProfScope ps(h, SMCPHYS_K_GATHER);
   LAUNCH(k_gather, nblk(n, 256), 256, h->stream, h->B, h->ctl, n);
   LAUNCH(k_gather_hist, dim3(nblk(n, 256), (unsigned)(t + 1)), 256, h->stream, h->B, h->ctl, n);
   return 0;
@@ -866,6 +925,7 @@ int smcphys_pf_rejuvenate(smcphys_handle* h, int32_t t, int32_t R, uint64_t* d_a
   if (R == 0) return 0;
   const int64_t n = h->cfg.num_particles;
   u64* acc = d_accept_count ? (u64*)d_accept_count : h->d_acc + t;
+  ProfScope ps(h, SMCPHYS_K_REJUVENATE);
   if (h->cfg.shape == SMCPHYS_SPHERE)
     LAUNCH(k_rejuvenate<SHAPE_SPHERE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B, h->ctl, h->tp, h->sp, n,
            h->cfg.particle_offset, h->cfg.seed, t, h->cfg.substeps, R, h->cfg.proposal_sigma, acc);
@@ -1059,6 +1119,7 @@ int smcphys_pf_pack(smcphys_handle* h, int32_t t, const double* d_global_max, ui
   if (count == 0) return 0;
   if (!d_send) return fail(SMCPHYS_EINVAL, "pf_pack: NULL send buffer");
   u64 U0 = (u64)(u0 * 4294967296.0);
+  ProfScope ps(h, SMCPHYS_K_GATHER);
   LAUNCH(k_cdf, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, d_global_max, n, (u64)W_before, 0);
   const int64_t words = 17 + 3 * (int64_t)(t + 1);
   // a shard's offspring can outnumber its particles; the index scratch holds n, so go in slabs of n
@@ -1086,6 +1147,7 @@ int smcphys_pf_unpack(smcphys_handle* h, int32_t t, const float* d_recv, int32_t
     total += counts[c];
   }
   if (total != n) return fail(SMCPHYS_EINVAL, "pf_unpack: chunks must fill every local slot exactly once");
+  ProfScope ps(h, SMCPHYS_K_GATHER);
   for (int c = 0; c < n_chunks; c++) {
     if (counts[c] == 0) continue;
     LAUNCH(k_unpack, dim3(nblk(counts[c], 256), (unsigned)(t + 2)), 256, h->stream, h->B, h->ctl, n,
