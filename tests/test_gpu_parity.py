@@ -83,14 +83,24 @@ def test_T1_trajectories_identical_noise(sp, shape, S, tol):
     mu_o, lp_o, st_o = orc.simulate(shape, S, INIT_POS, INIT_VEL, e, xt, f32=True, threads=8)
     err = np.abs(mu_g.astype(np.float64) - mu_o).max(axis=(0, 1))
     agree = err < tol
-    # a contact-branch flip (in / out of the breaking threshold, restitution threshold) sends the two float32
-    # evaluations down different branches; those particles are counted, not compared
-    assert agree.mean() > 0.90, (agree.mean(), np.sort(err)[-10:])
+    # a contact-branch flip (in / out of the breaking threshold, restitution threshold, a different deepest
+    # corner of the cube) sends two float32 evaluations down different branches; those particles are counted, not
+    # compared.  The yardstick for how many may flip is the oracle itself: its float32 mode against its float64
+    # mode on the same inputs (sphere: none flip; cube: ~19 % do over 120 steps — a tumbling cube is chaotic at
+    # float32 resolution).  The GPU must agree with the float32 oracle at least as often, minus 5 points.
+    mu_64 = orc.simulate(shape, S, INIT_POS, INIT_VEL, e, xt, f32=False, threads=8)[0]
+    yard = (np.abs(mu_o.astype(np.float64) - mu_64).max(axis=(0, 1)) < tol).mean()
+    assert agree.mean() > min(0.90, yard - 0.05), (agree.mean(), yard, np.sort(err)[-10:])
+    # before its first flip a particle is within tolerance at every step by construction; the flips must not
+    # cluster early (they need contacts to happen): at least 95 % of particles agree over the first 40 steps
+    early = np.abs(mu_g[:40].astype(np.float64) - mu_o[:40]).max(axis=(0, 1)) < tol
+    assert early.mean() > 0.95, early.mean()
     assert np.median(err) < 2e-5
     # transition log density of the agreeing particles
     rel = np.abs(lp_g[agree] - lp_o[agree]) / (1.0 + np.abs(lp_o[agree]))
     assert rel.max() < 1e-2 and np.median(rel) < 1e-5
-    print("T1 shape=%d S=%d: agree %.4f, median err %.2e" % (shape, S, agree.mean(), np.median(err)))
+    print("T1 shape=%d S=%d: agree %.4f (oracle f32-vs-f64 yardstick %.4f), median err %.2e"
+          % (shape, S, agree.mean(), yard, np.median(err)))
 
 
 def test_simulate_edge_cases(sp):
@@ -143,7 +153,9 @@ def test_T3_weight_sums_exact_and_textbook_agreement(sp):
         assert abs(g["ess"] - o["ess"]) <= 1e-12 * o["ess"] and abs(g["lse"] - o["lse"]) <= 1e-12
         # float64 textbook definitions
         w = np.exp(lw - lw.max())
-        assert abs(g["ess"] - w.sum() ** 2 / (w * w).sum()) < 2e-4 * g["ess"]
+        # ESS uses 19-bit weights (q >> 20) so that the sum of squares stays below 2^63 at N = 2^24: each weight
+        # loses < 2^-19 of the largest one, hence the relative error bound 2 n 2^-19 / sum(w)
+        assert abs(g["ess"] - w.sum() ** 2 / (w * w).sum()) < (2e-4 + 2 * n * 2.0 ** -19 / w.sum()) * g["ess"]
         assert abs(g["lse"] - (lw.max() + np.log(w.sum()))) < 1e-9
     # the integer CDF picks the same ancestors as the float64 cumulative sum (ties have measure zero)
     lw = rng.normal(0, 2, 20000)
@@ -230,3 +242,31 @@ def test_call_order_errors(sp):
         pf.run_smc()
         e = pf.get_particles(want_score=False)["e"]
         assert e.min() > 0 and e.max() < 1
+
+
+# ------------------------------------------------------------------ sharded filter (phase API) on one GPU
+@pytest.mark.parametrize("shape,G,n", [(0, 2, 500), (0, 4, 256), (1, 3, 200)])
+def test_sharded_phases_bit_identical_to_single_shard(sp, shape, G, n):
+    """G shards of n particles driven through smcphys_pf_* (pack / exchange / unpack migration) hold exactly the
+    particles of the unsharded filter with N = G n: same elasticities, log weights, decisions, bit for bit."""
+    from smc_physics_b200.sharded import LocalShards
+    T, R = 25, 2
+    path = _truth_path(shape, 0.6, T)
+    with sp.ParticleFilter(num_particles=G * n, shape=shape, substeps=5, max_timesteps=T, seed=21) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        stats = pf.run_smc(R=R)
+        one = pf.get_particles(want_traj=True)
+    sh = LocalShards(n, G, shape=shape, substeps=5, max_timesteps=T, seed=21)
+    try:
+        sh.set_trial(INIT_POS, INIT_VEL, path)
+        st2 = sh.run_smc(R=R)
+        many = sh.get_particles(want_traj=True)
+    finally:
+        sh.close()
+    assert sum(s["resampled"] for s in stats) >= 2                  # the migration path actually ran
+    assert [s["resampled"] for s in stats] == [s["resampled"] for s in st2]
+    assert np.array_equal(one["e"], many["e"])
+    assert np.array_equal(one["log_w"], many["log_w"])
+    assert np.array_equal(one["score"], many["score"])
+    assert np.array_equal(one["traj"], many["traj"])
+    assert np.allclose([s["ess"] for s in stats], [s["ess"] for s in st2], rtol=1e-12)
