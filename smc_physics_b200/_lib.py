@@ -3,7 +3,8 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO = os.path.join(HERE, "libsmcphys.so")
+# SMCPHYS_SO points at an alternative build of the same library (kernel tuning experiments)
+SO = os.environ.get("SMCPHYS_SO") or os.path.join(HERE, "libsmcphys.so")
 
 SPHERE, CUBE = 0, 1
 

@@ -321,48 +321,324 @@ __device__ __forceinline__ void solve_contacts(const Contact* c, int nc, float r
   w = w + dw;
 }
 
+// ---------------------------------------------------------------- sphere: single-contact fast path
+// For a sphere the contact arm is r = -h n, so r x n = 0 and the three rows of one contact (normal, two
+// tangents) are mutually decoupled: J_n M^-1 J_t^T = n.t / m = 0 and J_t1 M^-1 J_t2^T = h^2 (n x t1).(n x t2) / I = 0.
+// The projected Gauss-Seidel sweep therefore converges in its first iteration (the oracle's second sweep only
+// confirms a residual at rounding level and exits), and the solve is closed form:
+//   lambda_n = max(0, rhs_n),  (lambda_t1, lambda_t2) = cone-clamp(-relv_t / (1/m + h^2/I), mu lambda_n).
+// Two or more simultaneous contacts (edges, corners of the arena) couple through friction and take the general
+// solver, out of line.
+struct SphereHit {
+  int nc;
+  f3 n;
+  float dist;
+};
+
+__device__ __forceinline__ void sphere_vs_box(const f3& x, const f3& c, const f3& h, SphereHit& hit) {
+  f3 cb = x - c;
+  f3 hc = mk3(h.x - PH_BOX_MARGIN, h.y - PH_BOX_MARGIN, h.z - PH_BOX_MARGIN);
+  f3 p = mk3(fminf(fmaxf(cb.x, -hc.x), hc.x), fminf(fmaxf(cb.y, -hc.y), hc.y), fminf(fmaxf(cb.z, -hc.z), hc.z));
+  f3 df = cb - p;
+  float d2 = dot3(df, df);
+  f3 n;
+  float dist;
+  if (d2 > 0.f) {
+    float dl = sqrtf(d2);
+    n = df * (1.0f / dl);
+    dist = dl - PH_H - PH_BOX_MARGIN;
+  } else {
+    int ax = 0;
+    float best = h.x - fabsf(cb.x);
+    float dy = h.y - fabsf(cb.y), dz = h.z - fabsf(cb.z);
+    if (dy < best) { best = dy; ax = 1; }
+    if (dz < best) { best = dz; ax = 2; }
+    n = mk3(0.f, 0.f, 0.f);
+    setc3(n, ax, comp3(cb, ax) >= 0.f ? 1.f : -1.f);
+    dist = -(best + PH_H);
+  }
+  if (dist < PH_THR) {
+    if (hit.nc == 0) { hit.n = n; hit.dist = dist; }
+    hit.nc++;
+  }
+}
+
+// Contacts of the sphere: count, and the contact itself when there is exactly one.  Only the wall on the
+// body's side of each axis can be within reach (the opposite one is > 0.9 m away), so three box tests suffice.
+__device__ __forceinline__ void sphere_hits(const ScenePar& sp, const f3& x, SphereHit& hit) {
+  const float reach = PH_H + PH_THR;  // a box farther than this along any axis cannot touch
+  hit.nc = 0;
+  float d = x.z - PH_H;
+  if (d < PH_THR) { hit.nc = 1; hit.n = mk3(0.f, 0.f, 1.f); hit.dist = d; }
+  if (fabsf(x.x) > 0.5f - reach) sphere_vs_box(x, mk3(x.x >= 0.f ? 0.51f : -0.51f, 0.f, 0.51f), mk3(0.01f, 0.5f, 0.5f), hit);
+  if (fabsf(x.y) > 0.5f - reach) sphere_vs_box(x, mk3(0.f, x.y >= 0.f ? 0.51f : -0.51f, 0.51f), mk3(0.5f, 0.01f, 0.5f), hit);
+  if (x.z > 1.01f - sp.ceil_half - reach) sphere_vs_box(x, mk3(0.f, 0.f, 1.01f), mk3(0.5f, 0.5f, sp.ceil_half), hit);
+}
+
+__device__ __forceinline__ void sphere_solve_one(const SphereHit& hit, float restitution, f3& v, f3& w) {
+  const float inv_i = PH_INV_I_SPHERE;
+  const float dinv_t = 1.0f / (PH_INV_M + PH_H * PH_H * PH_INV_I_SPHERE);  // 1 / 3.5
+  f3 t1, t2;
+  plane_space(hit.n, t1, t2);
+  const f3 r = hit.n * (-PH_H);
+  const f3 rx1 = cross3(r, t1), rx2 = cross3(r, t2);
+  const float vn = dot3(hit.n, v);
+  const float vt1 = dot3(t1, v) + dot3(rx1, w), vt2 = dot3(t2, v) + dot3(rx2, w);
+  float rest = 0.f;
+  if (fabsf(vn) >= PH_REST_THRESH) rest = fmaxf(0.f, -(restitution * PH_STATIC_REST) * vn);
+  const float distance = hit.dist + PH_SLOP;
+  float verr = rest - vn, perr = 0.f;
+  if (distance > 0.f) verr -= distance / PH_DT;
+  else perr = -distance * PH_ERP / PH_DT;
+  const float ln = fmaxf(0.f, perr + verr);  // 1 / (1/m) = 1
+  const float lim = PH_FRICTION * ln;
+  float l1 = -vt1 * dinv_t, l2 = -vt2 * dinv_t;
+  const float m2 = l1 * l1 + l2 * l2;
+  if (m2 > lim * lim) {
+    const float scl = lim / sqrtf(m2);
+    l1 *= scl;
+    l2 *= scl;
+  }
+  v = v + hit.n * ln + t1 * l1 + t2 * l2;
+  w = w + (rx1 * l1 + rx2 * l2) * inv_i;
+}
+
+// two or more contacts: the general narrow phase + projected Gauss-Seidel, kept out of the hot loop
+__device__ __noinline__ void sphere_solve_many(ScenePar sp, float restitution, Body* s) {
+  Contact c[PH_MAXC];
+  int nc = collide_sphere(sp, *s, c);
+  f3 v = s->v, w = s->w;
+  if (nc > 0) solve_contacts<SHAPE_SPHERE>(c, nc, restitution, v, w);
+  s->v = v;
+  s->w = w;
+}
+
+struct Body;
+__device__ __forceinline__ void apply_forces(Body& s);
+__device__ __forceinline__ void integrate_q(Body& s);
+// ---------------------------------------------------------------- sphere: multi-contact solve, block cooperative
+// Contacts of the sphere in the order the oracle / Bullet visits them: plane, then the boxes in creation order
+// (-x, +y, +x, -y, ceiling).  Only (n, dist) are kept; the arm is always -h n.
+__device__ __forceinline__ int sphere_contacts_ordered(const ScenePar& sp, const f3& x, f3* n, float* dist) {
+  const float reach = PH_H + PH_THR;
+  int nc = 0;
+  SphereHit h1;
+  float d = x.z - PH_H;
+  if (d < PH_THR) { n[nc] = mk3(0.f, 0.f, 1.f); dist[nc] = d; nc++; }
+  const bool xpos = x.x >= 0.f, ypos = x.y >= 0.f;
+  const bool nearx = fabsf(x.x) > 0.5f - reach, neary = fabsf(x.y) > 0.5f - reach;
+  const bool yfirst = xpos && ypos;  // box1 (+y) precedes box2 (+x)
+#pragma unroll
+  for (int pass = 0; pass < 2; pass++) {
+    const bool do_y = (pass == 0) == yfirst;
+    if (do_y ? neary : nearx) {
+      h1.nc = 0;
+      if (do_y) sphere_vs_box(x, mk3(0.f, ypos ? 0.51f : -0.51f, 0.51f), mk3(0.5f, 0.01f, 0.5f), h1);
+      else sphere_vs_box(x, mk3(xpos ? 0.51f : -0.51f, 0.f, 0.51f), mk3(0.01f, 0.5f, 0.5f), h1);
+      if (h1.nc) { n[nc] = h1.n; dist[nc] = h1.dist; nc++; }
+    }
+  }
+  if (x.z > 1.01f - sp.ceil_half - reach) {
+    h1.nc = 0;
+    sphere_vs_box(x, mk3(0.f, 0.f, 1.01f), mk3(0.5f, 0.5f, sp.ceil_half), h1);
+    if (h1.nc) { n[nc] = h1.n; dist[nc] = h1.dist; nc++; }
+  }
+  return nc;
+}
+
+// Projected Gauss-Seidel for exactly two sphere contacts, all rows in registers.  Same sweep order and exit rule
+// as solve_contacts (normal rows of both contacts, then the friction pairs; stop when the largest squared
+// velocity change of a sweep is <= 1e-7; at most 50 sweeps).  Uses r = -h n: r x n = 0, r x t1 = -h t2,
+// r x t2 = +h t1 for the btPlaneSpace1 basis (t2 = n x t1).
+__device__ __forceinline__ void sphere_solve_two(const f3* nn, const float* dd, float restitution, f3& v, f3& w) {
+  const float inv_i = PH_INV_I_SPHERE, h = PH_H;
+  const float dinv_t = 1.0f / (PH_INV_M + PH_H * PH_H * PH_INV_I_SPHERE), kt = 1.0f / dinv_t;
+  const float crest = restitution * PH_STATIC_REST;
+  f3 n[2], t1[2], t2[2];
+  float rhs[2][3], app[2][3];
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    n[i] = nn[i];
+    plane_space(n[i], t1[i], t2[i]);
+    const float vn = dot3(n[i], v);
+    const float vt1 = dot3(t1[i], v) - h * dot3(t2[i], w), vt2 = dot3(t2[i], v) + h * dot3(t1[i], w);
+    float rest = 0.f;
+    if (fabsf(vn) >= PH_REST_THRESH) rest = fmaxf(0.f, -crest * vn);
+    const float distance = dd[i] + PH_SLOP;
+    float verr = rest - vn, perr = 0.f;
+    if (distance > 0.f) verr -= distance / PH_DT;
+    else perr = -distance * PH_ERP / PH_DT;
+    rhs[i][0] = perr + verr;
+    rhs[i][1] = -vt1 * dinv_t;
+    rhs[i][2] = -vt2 * dinv_t;
+    app[i][0] = app[i][1] = app[i][2] = 0.f;
+  }
+  f3 dv = mk3(0.f, 0.f, 0.f), dw = mk3(0.f, 0.f, 0.f);
+  for (int it = 0; it < PH_ITERS; it++) {
+    float resid = 0.f;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      float dimp = rhs[i][0] - dot3(n[i], dv);
+      const float sum = app[i][0] + dimp;
+      if (sum < 0.f) { dimp = -app[i][0]; app[i][0] = 0.f; }
+      else app[i][0] = sum;
+      dv = dv + n[i] * dimp;
+      resid = fmaxf(resid, dimp * dimp);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const float lim = PH_FRICTION * app[i][0];
+      const float a1 = dot3(t1[i], dv) - h * dot3(t2[i], dw), a2 = dot3(t2[i], dv) + h * dot3(t1[i], dw);
+      float s1 = app[i][1] + (rhs[i][1] - a1 * dinv_t), s2 = app[i][2] + (rhs[i][2] - a2 * dinv_t);
+      const float l2 = s1 * s1 + s2 * s2;
+      if (l2 > lim * lim) {
+        const float scl = lim / sqrtf(l2);
+        s1 *= scl;
+        s2 *= scl;
+      }
+      const float d1 = s1 - app[i][1], d2 = s2 - app[i][2];
+      app[i][1] = s1;
+      app[i][2] = s2;
+      dv = dv + t1[i] * d1 + t2[i] * d2;
+      dw = dw + (t1[i] * d2 - t2[i] * d1) * (h * inv_i);
+      const float e1 = d1 * kt, e2 = d2 * kt;
+      resid = fmaxf(resid, fmaxf(e1 * e1, e2 * e2));
+    }
+    if (resid <= PH_RESID) break;
+  }
+  v = v + dv;
+  w = w + dw;
+}
+
+// three or four simultaneous contacts (arena corners): general solver, out of line
+__device__ __noinline__ void sphere_solve_generic(const f3* n, const float* dist, int nc, float restitution, f3* v,
+                                                  f3* w) {
+  Contact c[PH_MAXC];
+  for (int i = 0; i < nc; i++) { c[i].n = n[i]; c[i].r = n[i] * (-PH_H); c[i].dist = dist[i]; }
+  f3 vv = *v, ww = *w;
+  solve_contacts<SHAPE_SPHERE>(c, nc, restitution, vv, ww);
+  *v = vv;
+  *w = ww;
+}
+
+// Shared staging area of one thread block: the bodies that have two or more contacts in the current substep
+// are handed to the first threads of the block, so the expensive iterative solve runs in densely packed warps
+// while the rest of the block only waits at a barrier.
+template <int BLOCK>
+struct SphereCoop {
+  float x[3][BLOCK], v[3][BLOCK], w[3][BLOCK], e[BLOCK];
+  int list[BLOCK];
+  int cnt;
+};
+
+template <int BLOCK>
+__device__ __forceinline__ void sphere_coop_solve(const ScenePar& sp, SphereCoop<BLOCK>& sh, bool many, float e, Body& s) {
+  const int total = __syncthreads_count(many);
+  if (total == 0) return;
+  const int tid = threadIdx.x;
+  if (many) {
+    const int slot = atomicAdd(&sh.cnt, 1);
+    sh.list[slot] = tid;
+    sh.x[0][tid] = s.x.x; sh.x[1][tid] = s.x.y; sh.x[2][tid] = s.x.z;
+    sh.v[0][tid] = s.v.x; sh.v[1][tid] = s.v.y; sh.v[2][tid] = s.v.z;
+    sh.w[0][tid] = s.w.x; sh.w[1][tid] = s.w.y; sh.w[2][tid] = s.w.z;
+    sh.e[tid] = e;
+  }
+  __syncthreads();
+  if (tid < total) {
+    const int p = sh.list[tid];
+    const f3 x = mk3(sh.x[0][p], sh.x[1][p], sh.x[2][p]);
+    f3 v = mk3(sh.v[0][p], sh.v[1][p], sh.v[2][p]), w = mk3(sh.w[0][p], sh.w[1][p], sh.w[2][p]);
+    f3 n[4];
+    float dist[4];
+    const int nc = sphere_contacts_ordered(sp, x, n, dist);
+    if (nc == 2) {
+      sphere_solve_two(n, dist, sh.e[p], v, w);
+    } else {
+      sphere_solve_generic(n, dist, nc, sh.e[p], &v, &w);
+    }
+    sh.v[0][p] = v.x; sh.v[1][p] = v.y; sh.v[2][p] = v.z;
+    sh.w[0][p] = w.x; sh.w[1][p] = w.y; sh.w[2][p] = w.z;
+  }
+  __syncthreads();
+  if (many) {
+    s.v = mk3(sh.v[0][tid], sh.v[1][tid], sh.v[2][tid]);
+    s.w = mk3(sh.w[0][tid], sh.w[1][tid], sh.w[2][tid]);
+  }
+  if (tid == 0) sh.cnt = 0;  // the next atomicAdd comes after the next __syncthreads_count
+}
+
+// One sphere substep executed by every thread of the block in lockstep.
+template <int BLOCK, bool TRACK_Q>
+__device__ __forceinline__ void substep_sphere_coop(const ScenePar& sp, SphereCoop<BLOCK>& sh, float e, Body& s) {
+  SphereHit hit;
+  hit.nc = 0;
+  if (!body_clear<SHAPE_SPHERE>(s.x, sp.ceil_half)) sphere_hits(sp, s.x, hit);
+  apply_forces(s);
+  if (hit.nc == 1) sphere_solve_one(hit, e, s.v, s.w);
+  sphere_coop_solve<BLOCK>(sp, sh, hit.nc > 1, e, s);
+  s.x = s.x + s.v * PH_DT;
+  if (TRACK_Q) integrate_q(s);
+}
+
 // ---------------------------------------------------------------- one 1/240 s substep (Bullet stepSimulation)
 // Order (pinned by the reference's PyBullet cube fixture, see oracle/smc_oracle.hpp): narrow phase at the
 // current pose; v += dt (g - k v (1 + |v|)), same drag on omega; contact solve; x += dt v; q <- exp(w dt/2) q.
 // TRACK_Q = false drops the orientation update: a sphere's orientation never feeds back into its motion,
 // so the particle-filter kernels do not carry it (PhySMC.forward_step on a batch does).
+__device__ __forceinline__ void apply_forces(Body& s) {
+  const float dt = PH_DT;
+  float vn = sqrtf(dot3(s.v, s.v));
+  float f = PH_DAMP * (1.0f + vn);
+  s.v = mk3(s.v.x + dt * (-f * s.v.x), s.v.y + dt * (-f * s.v.y), s.v.z + dt * (PH_G - f * s.v.z));
+  float wn = sqrtf(dot3(s.w, s.w));
+  float fw = PH_DAMP * (1.0f + wn);
+  s.w = mk3(s.w.x + dt * (-fw * s.w.x), s.w.y + dt * (-fw * s.w.y), s.w.z + dt * (-fw * s.w.z));
+}
+
+__device__ __forceinline__ void integrate_q(Body& s) {
+  const float dt = PH_DT;
+  float ang = sqrtf(dot3(s.w, s.w));
+  if (ang * dt > PH_ANG_THRESH) ang = 0.5f * 1.57079632679489661923f / dt;
+  f3 ax;
+  if (ang < 0.001f) ax = s.w * (0.5f * dt - (dt * dt * dt) * 0.020833333333f * ang * ang);
+  else ax = s.w * (sinf(0.5f * ang * dt) / ang);
+  float cw = cosf(ang * dt * 0.5f);
+  f4 q = s.q, r;
+  r.x = cw * q.x + ax.x * q.w + ax.y * q.z - ax.z * q.y;
+  r.y = cw * q.y - ax.x * q.z + ax.y * q.w + ax.z * q.x;
+  r.z = cw * q.z + ax.x * q.y - ax.y * q.x + ax.z * q.w;
+  r.w = cw * q.w - ax.x * q.x - ax.y * q.y - ax.z * q.z;
+  float inv = 1.0f / sqrtf(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w);
+  s.q.x = r.x * inv; s.q.y = r.y * inv; s.q.z = r.z * inv; s.q.w = r.w * inv;
+}
+
 template <int SHAPE, bool TRACK_Q>
 __device__ __forceinline__ void substep(const ScenePar& sp, float restitution, Body& s, Manifold& pm) {
   const float dt = PH_DT;
-  Contact c[PH_MAXC];
-  int nc = 0;
   const bool clear = body_clear<SHAPE>(s.x, sp.ceil_half);
-  if (!clear) {
-    if (SHAPE == SHAPE_SPHERE) nc = collide_sphere(sp, s, c);
-    else nc = collide_cube(sp, s, pm, c);
-  } else if (SHAPE == SHAPE_CUBE) {
-    pm.n = 0;
+  if (SHAPE == SHAPE_SPHERE) {
+    SphereHit hit;
+    hit.nc = 0;
+    if (!clear) sphere_hits(sp, s.x, hit);
+    if (hit.nc > 1) {
+      // the narrow phase of the general path runs at the pre-force pose / velocities, as in the oracle
+      apply_forces(s);
+      sphere_solve_many(sp, restitution, &s);
+    } else {
+      apply_forces(s);
+      if (hit.nc == 1) sphere_solve_one(hit, restitution, s.v, s.w);
+    }
+  } else {
+    Contact c[PH_MAXC];
+    int nc = 0;
+    if (!clear) nc = collide_cube(sp, s, pm, c);
+    else pm.n = 0;
+    apply_forces(s);
+    if (nc > 0) solve_contacts<SHAPE>(c, nc, restitution, s.v, s.w);
   }
-  {
-    float vn = sqrtf(dot3(s.v, s.v));
-    float f = PH_DAMP * (1.0f + vn);
-    s.v = mk3(s.v.x + dt * (-f * s.v.x), s.v.y + dt * (-f * s.v.y), s.v.z + dt * (PH_G - f * s.v.z));
-    float wn = sqrtf(dot3(s.w, s.w));
-    float fw = PH_DAMP * (1.0f + wn);
-    s.w = mk3(s.w.x + dt * (-fw * s.w.x), s.w.y + dt * (-fw * s.w.y), s.w.z + dt * (-fw * s.w.z));
-  }
-  if (nc > 0) solve_contacts<SHAPE>(c, nc, restitution, s.v, s.w);
   s.x = s.x + s.v * dt;
-  if (TRACK_Q || SHAPE == SHAPE_CUBE) {
-    float ang = sqrtf(dot3(s.w, s.w));
-    if (ang * dt > PH_ANG_THRESH) ang = 0.5f * 1.57079632679489661923f / dt;
-    f3 ax;
-    if (ang < 0.001f) ax = s.w * (0.5f * dt - (dt * dt * dt) * 0.020833333333f * ang * ang);
-    else ax = s.w * (sinf(0.5f * ang * dt) / ang);
-    float cw = cosf(ang * dt * 0.5f);
-    f4 q = s.q, r;
-    r.x = cw * q.x + ax.x * q.w + ax.y * q.z - ax.z * q.y;
-    r.y = cw * q.y - ax.x * q.z + ax.y * q.w + ax.z * q.x;
-    r.z = cw * q.z + ax.x * q.y - ax.y * q.x + ax.z * q.w;
-    r.w = cw * q.w - ax.x * q.x - ax.y * q.y - ax.z * q.z;
-    float inv = 1.0f / sqrtf(r.x * r.x + r.y * r.y + r.z * r.z + r.w * r.w);
-    s.q.x = r.x * inv; s.q.y = r.y * inv; s.q.z = r.z * inv; s.q.w = r.w * inv;
-  }
+  if (TRACK_Q || SHAPE == SHAPE_CUBE) integrate_q(s);
 }
 
 // PhySMC.step = sync! ; forward_step (PhySMC.jl:32-35): the body is re-posed, so the contact cache starts

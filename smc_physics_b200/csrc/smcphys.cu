@@ -402,6 +402,42 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
   return qs;
 }
 
+// Sphere version for the rejuvenation kernel: the whole thread block steps in lockstep so that bodies with
+// several simultaneous contacts can be solved in compacted warps (physics.cuh, SphereCoop).  No orientation.
+#ifndef RJ_BLOCK
+#define RJ_BLOCK 256
+#endif
+#ifndef RJ_MINB
+#define RJ_MINB 3  // blocks per SM the register allocation must allow
+#endif
+template <bool TRACK_Q, bool TRAJ>
+__device__ __forceinline__ double resimulate_sphere_coop(const ScenePar& sp, const TrialPar& tp, int S, float e,
+                                                         const float* __restrict__ xt, int64_t n, int64_t i, int steps,
+                                                         Body& s, SphereCoop<RJ_BLOCK>& sh, float* traj, bool live) {
+  init_body(tp, s);
+  double qs = 0.0;
+  const float* p = xt + i;
+  float nx = p[0], ny = p[n], nz = p[2 * n];
+  for (int k = 0; k < steps; k++) {
+    const float x = nx, y = ny, z = nz;
+    if (k + 1 < steps) {
+      const float* pn = p + (int64_t)(k + 1) * 3 * n;
+      nx = pn[0]; ny = pn[n]; nz = pn[2 * n];
+    }
+    if (k >= 1) {
+      float dx = x - s.x.x, dy = y - s.x.y, dz = z - s.x.z;
+      qs += (double)(dx * dx + dy * dy + dz * dz);
+    }
+    s.x = mk3(x, y, z);
+    for (int j = 0; j < S; j++) substep_sphere_coop<RJ_BLOCK, TRACK_Q>(sp, sh, e, s);
+    if (TRAJ && live) {
+      float* o = traj + (int64_t)k * 3 * n + i;
+      o[0] = s.x.x; o[n] = s.x.y; o[2 * n] = s.x.z;
+    }
+  }
+  return qs;
+}
+
 // ---------------------------------------------------------------- K5: rejuvenation (re-simulate + MH)
 // for i = 1:N, j = 1:R: Gen.mh(trace_i, proposal, ())  (Inference/particle_filter.jl:58-62):
 //   e' ~ TruncNorm(e, 0.1, 0, 1) (proposal :17-29, Utilities/truncatednorm.jl:11-16); re-simulate steps 1..t+1
@@ -409,13 +445,21 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
 //   + log q(e|e').  The observation terms and the s = 1 term cancel; the PF log weight is untouched.
 // One thread per particle, the R moves of a particle form a chain and run back to back in registers.
 template <int SHAPE>
-__global__ void __launch_bounds__(PF_BLOCK) k_rejuvenate(Bufs B, const Ctl* ctl, TrialPar tp, ScenePar sp, int64_t n,
-                                                         int64_t goff, u64 seed, int t, int S, int R, double prop_sigma,
-                                                         u64* accept_out) {
+__global__ void __launch_bounds__(SHAPE == SHAPE_SPHERE ? RJ_BLOCK : PF_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : 1)
+    k_rejuvenate(Bufs B, const Ctl* ctl, TrialPar tp, ScenePar sp, int64_t n, int64_t goff, u64 seed, int t, int S,
+                 int R, double prop_sigma, u64* accept_out) {
+  __shared__ SphereCoop<SHAPE == SHAPE_SPHERE ? RJ_BLOCK : 1> sh;
+  if (SHAPE == SHAPE_SPHERE) {
+    if (threadIdx.x == 0) sh.cnt = 0;
+    __syncthreads();
+  }
   const int cur = ctl->cur ^ ctl->resampled;
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  // the sphere path steps the block in lockstep: tail threads shadow the last particle and store nothing
+  const bool live = i0 < n;
+  const int64_t i = (SHAPE == SHAPE_SPHERE && !live) ? n - 1 : i0;
   unsigned int acc = 0;
-  if (i < n) {
+  if (SHAPE == SHAPE_SPHERE || live) {
     double e_old = B.e[cur][i], q_old = B.qs[cur][i];
     const double inv2s2 = 0.5 / (tp.sigma_tr * tp.sigma_tr);
     Body keep;
@@ -427,12 +471,16 @@ __global__ void __launch_bounds__(PF_BLOCK) k_rejuvenate(Bufs B, const Ctl* ctl,
       double fwd = truncnorm_logpdf(e_new, e_old, prop_sigma, 0.0, 1.0);
       double bwd = truncnorm_logpdf(e_old, e_new, prop_sigma, 0.0, 1.0);
       Body s;
-      double q_new = resimulate<SHAPE, SHAPE == SHAPE_CUBE, false>(sp, tp, S, (float)e_new, B.xt[cur], n, i, t + 1, s,
-                                                                   nullptr);
+      double q_new;
+      if (SHAPE == SHAPE_SPHERE)
+        q_new = resimulate_sphere_coop<false, false>(sp, tp, S, (float)e_new, B.xt[cur], n, i, t + 1, s,
+                                                     *reinterpret_cast<SphereCoop<RJ_BLOCK>*>(&sh), nullptr, live);
+      else
+        q_new = resimulate<SHAPE, true, false>(sp, tp, S, (float)e_new, B.xt[cur], n, i, t + 1, s, nullptr);
       double alpha = -(q_new - q_old) * inv2s2 - fwd + bwd;
       if (log(u01(r[1])) < alpha) { e_old = e_new; q_old = q_new; keep = s; any = true; acc++; }
     }
-    if (any) {
+    if (any && live) {
       B.e[cur][i] = e_old;
       B.qs[cur][i] = q_old;
       float* st = B.st[cur];
@@ -442,6 +490,7 @@ __global__ void __launch_bounds__(PF_BLOCK) k_rejuvenate(Bufs B, const Ctl* ctl,
       }
       store_body(st, n, i, keep);
     }
+    if (!live) acc = 0;
   }
   if (accept_out) {
 #pragma unroll
@@ -452,17 +501,31 @@ __global__ void __launch_bounds__(PF_BLOCK) k_rejuvenate(Bufs B, const Ctl* ctl,
 
 // ---------------------------------------------------------------- getters / stateless kernels
 template <int SHAPE>
-__global__ void __launch_bounds__(PF_BLOCK) k_traj(const double* e, const float* xt, TrialPar tp, ScenePar sp,
-                                                   int64_t n, int S, int T, float* mu_out, double* q_out,
-                                                   float* state_out) {
-  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= n) return;
+__global__ void __launch_bounds__(SHAPE == SHAPE_SPHERE ? RJ_BLOCK : PF_BLOCK)
+    k_traj(const double* e, const float* xt, TrialPar tp, ScenePar sp, int64_t n, int S, int T, float* mu_out,
+           double* q_out, float* state_out) {
+  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const bool live = i0 < n;
   Body s;
   double qs;
-  if (mu_out) qs = resimulate<SHAPE, true, true>(sp, tp, S, (float)e[i], xt, n, i, T, s, mu_out);
-  else qs = resimulate<SHAPE, true, false>(sp, tp, S, (float)e[i], xt, n, i, T, s, nullptr);
-  if (q_out) q_out[i] = qs;
-  if (state_out) store_body(state_out, n, i, s);
+  if (SHAPE == SHAPE_SPHERE) {
+    // same block-cooperative stepping as the rejuvenation kernel (plus orientation): tail threads shadow
+    // the last particle so that the whole block reaches every barrier
+    __shared__ SphereCoop<SHAPE == SHAPE_SPHERE ? RJ_BLOCK : 1> sh;
+    if (threadIdx.x == 0) sh.cnt = 0;
+    __syncthreads();
+    const int64_t i = live ? i0 : n - 1;
+    SphereCoop<RJ_BLOCK>& shr = *reinterpret_cast<SphereCoop<RJ_BLOCK>*>(&sh);
+    if (mu_out) qs = resimulate_sphere_coop<true, true>(sp, tp, S, (float)e[i], xt, n, i, T, s, shr, mu_out, live);
+    else qs = resimulate_sphere_coop<true, false>(sp, tp, S, (float)e[i], xt, n, i, T, s, shr, nullptr, live);
+  } else {
+    if (!live) return;
+    if (mu_out) qs = resimulate<SHAPE, true, true>(sp, tp, S, (float)e[i0], xt, n, i0, T, s, mu_out);
+    else qs = resimulate<SHAPE, true, false>(sp, tp, S, (float)e[i0], xt, n, i0, T, s, nullptr);
+  }
+  if (!live) return;
+  if (q_out) q_out[i0] = qs;
+  if (state_out) store_body(state_out, n, i0, s);
 }
 
 // score = log joint of the trace: sum_s logN(x~_s; mu_s, sigma_tr) + sum_s logN(y_s; x~_s, sigma_obs); the
@@ -927,7 +990,7 @@ int smcphys_pf_rejuvenate(smcphys_handle* h, int32_t t, int32_t R, uint64_t* d_a
   u64* acc = d_accept_count ? (u64*)d_accept_count : h->d_acc + t;
   ProfScope ps(h, SMCPHYS_K_REJUVENATE);
   if (h->cfg.shape == SMCPHYS_SPHERE)
-    LAUNCH(k_rejuvenate<SHAPE_SPHERE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B, h->ctl, h->tp, h->sp, n,
+    LAUNCH(k_rejuvenate<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B, h->ctl, h->tp, h->sp, n,
            h->cfg.particle_offset, h->cfg.seed, t, h->cfg.substeps, R, h->cfg.proposal_sigma, acc);
   else
     LAUNCH(k_rejuvenate<SHAPE_CUBE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B, h->ctl, h->tp, h->sp, n,
@@ -995,7 +1058,7 @@ int smcphys_get_particles(smcphys_handle* h, double* e, double* log_w, double* s
     // the other history buffer is free between steps: rows 0..T-1 of it receive the simulator outputs
     float* d = h->B.xt[cur ^ 1];
     if (h->cfg.shape == SMCPHYS_SPHERE)
-      LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
+      LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
              h->cfg.substeps, T, d, (double*)nullptr, (float*)nullptr);
     else
       LAUNCH(k_traj<SHAPE_CUBE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
@@ -1020,7 +1083,7 @@ int smcphys_get_states(smcphys_handle* h, float* state13) {
   if (h->steps_done == 0) {
     soa = h->B.st[cur];
   } else if (h->cfg.shape == SMCPHYS_SPHERE) {
-    LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
+    LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
            h->cfg.substeps, h->steps_done, (float*)nullptr, (double*)nullptr, soa);
   } else {
     LAUNCH(k_traj<SHAPE_CUBE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
@@ -1231,7 +1294,7 @@ int smcphys_simulate(int32_t device, int32_t shape, int32_t S, double ceiling_ha
   if (T > 0) CK(cudaMemcpyAsync(d_xt, xt, sizeof(float) * 3 * (size_t)T * n, cudaMemcpyHostToDevice, st));
   LAUNCH(k_f2d, nblk(n, 256), 256, st, d_e, d_ed, n);
   if (shape == SMCPHYS_SPHERE)
-    LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, PF_BLOCK), PF_BLOCK, st, d_ed, d_xt, tp, sp, n, S, T, d_mu, d_q, d_soa);
+    LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, st, d_ed, d_xt, tp, sp, n, S, T, d_mu, d_q, d_soa);
   else
     LAUNCH(k_traj<SHAPE_CUBE>, nblk(n, PF_BLOCK), PF_BLOCK, st, d_ed, d_xt, tp, sp, n, S, T, d_mu, d_q, d_soa);
   if (mu_out && T > 0) CK(cudaMemcpyAsync(mu_out, d_mu, sizeof(float) * 3 * (size_t)T * n, cudaMemcpyDeviceToHost, st));
