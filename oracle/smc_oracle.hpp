@@ -42,6 +42,9 @@
 #include <atomic>
 
 namespace oracle {
+#ifdef ORACLE_COUNT_ITERS
+static long oracle_iter_hist[5][64];  // [min(nc,4)][sweeps used]: diagnostic builds only
+#endif
 
 // threads over particles (the analogue of the reference's pmap workers); dynamic chunks
 template <class F> inline void parallel_for(int64_t n, int threads, int64_t chunk, F fn) {
@@ -344,7 +347,13 @@ inline void substep(const Scene<T>& sc, int shape, T restitution, State<T>& s, P
       rhs[i][2] = -relv[2] * dinv[i][2];
     }
     V3<T> dv = {T(0), T(0), T(0)}, dw = {T(0), T(0), T(0)};
+#ifdef ORACLE_COUNT_ITERS
+    int iters_used = 0;
+#endif
     for (int it = 0; it < K<T>::iters(); it++) {
+#ifdef ORACLE_COUNT_ITERS
+      iters_used = it + 1;
+#endif
       T resid = T(0);
       for (int i = 0; i < nc; i++) {
         T dimp = rhs[i][0] - (dot(dir[i][0], dv) + dot(rxn[i][0], dw)) * dinv[i][0];
@@ -382,7 +391,13 @@ inline void substep(const Scene<T>& sc, int shape, T restitution, State<T>& s, P
     }
     s.v = s.v + dv;
     s.w = s.w + dw;
+#ifdef ORACLE_COUNT_ITERS
+    oracle_iter_hist[std::min(nc, 4)][iters_used]++;
+#endif
   }
+#ifdef ORACLE_COUNT_ITERS
+  else oracle_iter_hist[0][0]++;
+#endif
 
   // integrate pose: x += dt v ; q <- exp(w dt / 2) * q (btMultiBody::stepPositionsMultiDof)
   s.x = s.x + s.v * dt;
