@@ -47,7 +47,7 @@ struct Body {
 #define PH_REST_THRESH 0.2f               // restitutionVelocityThreshold
 #define PH_RESID 1e-7f                    // leastSquaresResidualThreshold
 #define PH_ITERS 50                       // numIterations
-#define PH_STALL 5e-7f                     // early exit of an infeasible solve: velocity change per sweep
+#define PH_STALL 1e-6f                     // early exit of an infeasible solve: velocity change per sweep
 #define PH_BOX_MARGIN 0.001f              // collision margin of a 0.01-thin btBoxShape
 #define PH_ANG_THRESH 0.78539816339744830962f
 #define PH_THR (0.02f * 1.7320508075688772f * PH_H)  // contact breaking threshold (0.02 x AABB radius)
@@ -478,12 +478,15 @@ __device__ __forceinline__ void sphere_solve_two(const f3* nn, const float* dd, 
   for (int it = 0; it < PH_ITERS; it++) {
     float resid = 0.f;
     const f3 pdv = dv, pdw = dw;
+    float dn[2];
+    bool steady = true;  // no projection touched this sweep and no friction row outgrows its cone
 #pragma unroll
     for (int i = 0; i < 2; i++) {
       float dimp = rhs[i][0] - dot3(n[i], dv);
       const float sum = app[i][0] + dimp;
-      if (sum < 0.f) { dimp = -app[i][0]; app[i][0] = 0.f; }
+      if (sum < 0.f) { dimp = -app[i][0]; app[i][0] = 0.f; steady = false; }
       else app[i][0] = sum;
+      dn[i] = dimp;
       dv = dv + n[i] * dimp;
       resid = fmaxf(resid, dimp * dimp);
     }
@@ -497,6 +500,7 @@ __device__ __forceinline__ void sphere_solve_two(const f3* nn, const float* dd, 
         const float scl = lim / sqrtf(l2);
         s1 *= scl;
         s2 *= scl;
+        steady = false;
       }
       const float d1 = s1 - app[i][1], d2 = s2 - app[i][2];
       app[i][1] = s1;
@@ -505,17 +509,25 @@ __device__ __forceinline__ void sphere_solve_two(const f3* nn, const float* dd, 
       dw = dw + (t1[i] * d2 - t2[i] * d1) * (h * inv_i);
       const float e1 = d1 * kt, e2 = d2 * kt;
       resid = fmaxf(resid, fmaxf(e1 * e1, e2 * e2));
+      const float grow = PH_FRICTION * dn[i];
+      steady = steady && (d1 * d1 + d2 * d2 <= grow * grow);
     }
     if (resid <= PH_RESID) break;
     // A body squeezed between (nearly) opposing faces - teleported under a wall, into the 1 cm gap between the
-    // wall boxes and the floor - has no feasible solution: the reference keeps sweeping to its 50-sweep cap,
-    // accumulating impulse on the opposing normal rows, while (dv, dw) converged geometrically (ratio ~0.2)
-    // within ~10 sweeps.  Only (dv, dw) leave the solver, so stop once a sweep moves them by < PH_STALL
-    // (m/s; the remaining sweeps would change the result by < 1.2e-7 m/s, below float32 resolution).
-    const f3 ddv = dv - pdv, ddw = dw - pdw;
-    const float mv = fmaxf(fmaxf(fabsf(ddv.x), fabsf(ddv.y)), fabsf(ddv.z));
-    const float mw = fmaxf(fmaxf(fabsf(ddw.x), fabsf(ddw.y)), fabsf(ddw.z)) * PH_H;
-    if (fmaxf(mv, mw) < PH_STALL) break;
+    // wall boxes and the floor - has no feasible solution.  The reference keeps sweeping to its 50-sweep cap:
+    // the impulses of the conflicting rows grow linearly for ever while (dv, dw), the only thing that leaves
+    // the solver, converged geometrically (ratio ~0.2) within ~10 sweeps.  An unprojected sweep is a fixed
+    // affine map of (dv, dw) alone, so once a sweep (a) leaves (dv, dw) where they were, (b) projected nothing
+    // (no normal impulse clamped at 0, no friction pair scaled back to its cone) and (c) grows every friction
+    // pair no faster than its cone mu * lambda_n grows, every later sweep repeats it exactly: stop.  A friction
+    // row that outgrows its cone (floor friction holding against a wall's push) will saturate in a later sweep
+    // and release the body, so that case keeps sweeping like the reference.
+    if (steady) {
+      const f3 ddv = dv - pdv, ddw = dw - pdw;
+      const float mv = fmaxf(fmaxf(fabsf(ddv.x), fabsf(ddv.y)), fabsf(ddv.z));
+      const float mw = fmaxf(fmaxf(fabsf(ddw.x), fabsf(ddw.y)), fabsf(ddw.z)) * PH_H;
+      if (fmaxf(mv, mw) < PH_STALL) break;
+    }
   }
   v = v + dv;
   w = w + dw;
