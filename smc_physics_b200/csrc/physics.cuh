@@ -111,42 +111,6 @@ __device__ __forceinline__ bool body_clear(const f3& x, float ceil_half) {
 }
 
 // ---------------------------------------------------------------- narrow phase
-// sphere: plane (support point) then the five boxes (closest point on the margin-shrunk core; centre inside
-// the core -> minimum-translation face of the full box).
-__device__ __forceinline__ int collide_sphere(const ScenePar& sp, const Body& s, Contact* out) {
-  int nc = 0;
-  float d = s.x.z - PH_H;
-  if (d < PH_THR) { out[nc].r = mk3(0.f, 0.f, -PH_H); out[nc].n = mk3(0.f, 0.f, 1.f); out[nc].dist = d; nc++; }
-#pragma unroll
-  for (int b = 0; b < 5; b++) {
-    f3 c, h;
-    static_box(b, sp.ceil_half, c, h);
-    f3 cb = s.x - c;
-    f3 hc = mk3(h.x - PH_BOX_MARGIN, h.y - PH_BOX_MARGIN, h.z - PH_BOX_MARGIN);
-    f3 p = mk3(fminf(fmaxf(cb.x, -hc.x), hc.x), fminf(fmaxf(cb.y, -hc.y), hc.y), fminf(fmaxf(cb.z, -hc.z), hc.z));
-    f3 df = cb - p;
-    float d2 = dot3(df, df);
-    f3 n;
-    float dist;
-    if (d2 > 0.f) {
-      float dl = sqrtf(d2);
-      n = df * (1.0f / dl);
-      dist = dl - PH_H - PH_BOX_MARGIN;
-    } else {
-      int ax = 0;
-      float best = h.x - fabsf(cb.x);
-      float dy = h.y - fabsf(cb.y), dz = h.z - fabsf(cb.z);
-      if (dy < best) { best = dy; ax = 1; }
-      if (dz < best) { best = dz; ax = 2; }
-      n = mk3(0.f, 0.f, 0.f);
-      setc3(n, ax, comp3(cb, ax) >= 0.f ? 1.f : -1.f);
-      dist = -(best + PH_H);
-    }
-    if (dist < PH_THR && nc < PH_MAXC) { out[nc].r = n * (-PH_H); out[nc].n = n; out[nc].dist = dist; nc++; }
-  }
-  return nc;
-}
-
 // cube: one deepest support vertex per substep into the persistent plane manifold (keyed on the body-local
 // corner, refreshed and pruned every substep), then face-vertex contacts against the five boxes along the
 // axis of least overlap (the documented modelling choice of the oracle; Bullet's btBoxBoxDetector is not
@@ -332,8 +296,10 @@ __device__ __forceinline__ void solve_contacts(const Contact* c, int nc, float r
 // solver, out of line.
 struct SphereHit {
   int nc;
-  f3 n;
+  f3 n;     // first contact
   float dist;
+  f3 n2;    // second contact (valid when nc >= 2)
+  float dist2;
 };
 
 __device__ __forceinline__ void sphere_vs_box(const f3& x, const f3& c, const f3& h, SphereHit& hit) {
@@ -360,6 +326,7 @@ __device__ __forceinline__ void sphere_vs_box(const f3& x, const f3& c, const f3
   }
   if (dist < PH_THR) {
     if (hit.nc == 0) { hit.n = n; hit.dist = dist; }
+    else if (hit.nc == 1) { hit.n2 = n; hit.dist2 = dist; }
     hit.nc++;
   }
 }
@@ -374,6 +341,19 @@ __device__ __forceinline__ void sphere_hits(const ScenePar& sp, const f3& x, Sph
   if (fabsf(x.x) > 0.5f - reach) sphere_vs_box(x, mk3(x.x >= 0.f ? 0.51f : -0.51f, 0.f, 0.51f), mk3(0.01f, 0.5f, 0.5f), hit);
   if (fabsf(x.y) > 0.5f - reach) sphere_vs_box(x, mk3(0.f, x.y >= 0.f ? 0.51f : -0.51f, 0.51f), mk3(0.5f, 0.01f, 0.5f), hit);
   if (x.z > 1.01f - sp.ceil_half - reach) sphere_vs_box(x, mk3(0.f, 0.f, 1.01f), mk3(0.5f, 0.5f, sp.ceil_half), hit);
+}
+
+// right-hand side of the normal row of one sphere contact (its effective mass is 1: r x n = 0, m = 1), i.e. the
+// normal impulse the contact would get on its own
+__device__ __forceinline__ float sphere_rhs_n(const f3& n, float dist, float restitution, const f3& v) {
+  const float vn = dot3(n, v);
+  float rest = 0.f;
+  if (fabsf(vn) >= PH_REST_THRESH) rest = fmaxf(0.f, -(restitution * PH_STATIC_REST) * vn);
+  const float distance = dist + PH_SLOP;
+  float verr = rest - vn, perr = 0.f;
+  if (distance > 0.f) verr -= distance / PH_DT;
+  else perr = -distance * PH_ERP / PH_DT;
+  return perr + verr;
 }
 
 __device__ __forceinline__ void sphere_solve_one(const SphereHit& hit, float restitution, f3& v, f3& w) {
@@ -404,14 +384,39 @@ __device__ __forceinline__ void sphere_solve_one(const SphereHit& hit, float res
   w = w + (rx1 * l1 + rx2 * l2) * inv_i;
 }
 
-// two or more contacts: the general narrow phase + projected Gauss-Seidel, kept out of the hot loop
-__device__ __noinline__ void sphere_solve_many(ScenePar sp, float restitution, Body* s) {
-  Contact c[PH_MAXC];
-  int nc = collide_sphere(sp, *s, c);
-  f3 v = s->v, w = s->w;
-  if (nc > 0) solve_contacts<SHAPE_SPHERE>(c, nc, restitution, v, w);
-  s->v = v;
-  s->w = w;
+// Contact response that needs no iteration, in line: one contact (closed form above), and the two-contact cases
+// the projected Gauss-Seidel solver leaves after one or two sweeps anyway (85-90 % of them in a filter run):
+//  * neither normal row pushes (rhs_n <= 0 for both: contacts within the breaking threshold but separating):
+//    sweep 1 clamps both normal impulses to 0, both friction cones are empty, the residual is 0 -> no impulse;
+//  * exactly one pushes and the other stays idle: sweep 1 gives the active contact its single-contact closed form
+//    (the idle contact's rows are all clamped to 0), sweep 2 repeats it to rounding and exits.  "Stays idle" is
+//    checked exactly as the solver would: the idle normal row against the active normal impulse alone (sweep 1)
+//    and against the full velocity change including friction (sweep 2).  If either check fails the velocities are
+//    restored and the body goes to the iterative solver.
+// The order of the two contacts does not matter in these cases.  Differences to the iterative result are at
+// rounding level (< 1e-6 m/s, tools/diag in DESIGN.md section 3.1).  Returns true when the body still needs the
+// iterative solver; otherwise v, w are final.
+__device__ __forceinline__ bool sphere_contacts_inline(SphereHit& hit, float restitution, f3& v, f3& w) {
+  bool many = hit.nc > 1, screen = false;
+  float r_idle = 0.f;
+  f3 n_idle = mk3(0.f, 0.f, 0.f);
+  if (hit.nc == 2) {
+    const float r0 = sphere_rhs_n(hit.n, hit.dist, restitution, v), r1 = sphere_rhs_n(hit.n2, hit.dist2, restitution, v);
+    if (r0 <= 0.f && r1 <= 0.f) return false;
+    if (r0 <= 0.f || r1 <= 0.f) {
+      float lam;
+      if (r0 > 0.f) { n_idle = hit.n2; r_idle = r1; lam = r0; }
+      else { n_idle = hit.n; r_idle = r0; lam = r1; hit.n = hit.n2; hit.dist = hit.dist2; }
+      screen = r_idle - dot3(n_idle, hit.n) * lam <= 0.f;
+    }
+  }
+  const f3 v0 = v, w0 = w;
+  if (hit.nc == 1 || screen) sphere_solve_one(hit, restitution, v, w);
+  if (screen) {
+    if (r_idle - dot3(n_idle, v - v0) <= 0.f) many = false;
+    else { v = v0; w = w0; }
+  }
+  return many;
 }
 
 struct Body;
@@ -544,68 +549,17 @@ __device__ __noinline__ void sphere_solve_generic(const f3* n, const float* dist
   *w = ww;
 }
 
-// Shared staging area of one thread block: the bodies that have two or more contacts in the current substep
-// are handed to the first threads of the block, so the expensive iterative solve runs in densely packed warps
-// while the rest of the block only waits at a barrier.
-template <int BLOCK>
-struct SphereCoop {
-  float x[3][BLOCK], v[3][BLOCK], w[3][BLOCK], e[BLOCK];
-  int list[BLOCK];
-  int cnt;
-};
-
-template <int BLOCK>
-__device__ __forceinline__ void sphere_coop_solve(const ScenePar& sp, SphereCoop<BLOCK>& sh, bool many, float e, Body& s) {
-  const int total = __syncthreads_count(many);
-  if (total == 0) return;
-  const int tid = threadIdx.x;
-  if (many) {
-    const int slot = atomicAdd(&sh.cnt, 1);
-    sh.list[slot] = tid;
-    sh.x[0][tid] = s.x.x; sh.x[1][tid] = s.x.y; sh.x[2][tid] = s.x.z;
-    sh.v[0][tid] = s.v.x; sh.v[1][tid] = s.v.y; sh.v[2][tid] = s.v.z;
-    sh.w[0][tid] = s.w.x; sh.w[1][tid] = s.w.y; sh.w[2][tid] = s.w.z;
-    sh.e[tid] = e;
-  }
-  __syncthreads();
-  if (tid < total) {
-    const int p = sh.list[tid];
-    const f3 x = mk3(sh.x[0][p], sh.x[1][p], sh.x[2][p]);
-    f3 v = mk3(sh.v[0][p], sh.v[1][p], sh.v[2][p]), w = mk3(sh.w[0][p], sh.w[1][p], sh.w[2][p]);
-    f3 n[4];
-    float dist[4];
-    const int nc = sphere_contacts_ordered(sp, x, n, dist);
-    if (nc == 2) {
-      sphere_solve_two(n, dist, sh.e[p], v, w);
-    } else {
-      sphere_solve_generic(n, dist, nc, sh.e[p], &v, &w);
-    }
-    sh.v[0][p] = v.x; sh.v[1][p] = v.y; sh.v[2][p] = v.z;
-    sh.w[0][p] = w.x; sh.w[1][p] = w.y; sh.w[2][p] = w.z;
-  }
-  __syncthreads();
-  if (many) {
-    s.v = mk3(sh.v[0][tid], sh.v[1][tid], sh.v[2][tid]);
-    s.w = mk3(sh.w[0][tid], sh.w[1][tid], sh.w[2][tid]);
-  }
-  if (tid == 0) sh.cnt = 0;  // the next atomicAdd comes after the next __syncthreads_count
-}
-
-// One sphere substep executed by every thread of the block in lockstep.
-template <int BLOCK, bool TRACK_Q>
-__device__ __forceinline__ void substep_sphere_coop(const ScenePar& sp, SphereCoop<BLOCK>& sh, float e, Body& s) {
-  SphereHit hit;
-  hit.nc = 0;
-  if (!body_clear<SHAPE_SPHERE>(s.x, sp.ceil_half)) sphere_hits(sp, s.x, hit);
-  apply_forces(s);
-#ifndef EXP_NO_ONE
-  if (hit.nc == 1) sphere_solve_one(hit, e, s.v, s.w);
-#endif
-#ifndef EXP_NO_MANY
-  sphere_coop_solve<BLOCK>(sp, sh, hit.nc > 1, e, s);
-#endif
-  s.x = s.x + s.v * PH_DT;
-  if (TRACK_Q) integrate_q(s);
+// Contacts that do need the iterative solver (10-15 % of the two-contact substeps of a filter run, and every
+// corner): out of line, so that the registers of the hot loop are sized by the free-flight / single-contact path.
+__device__ __noinline__ void sphere_solve_iter(ScenePar sp, float restitution, Body* s) {
+  f3 n[4];
+  float dist[4];
+  const int nc = sphere_contacts_ordered(sp, s->x, n, dist);
+  f3 v = s->v, w = s->w;
+  if (nc == 2) sphere_solve_two(n, dist, restitution, v, w);
+  else if (nc > 0) sphere_solve_generic(n, dist, nc, restitution, &v, &w);
+  s->v = v;
+  s->w = w;
 }
 
 // ---------------------------------------------------------------- one 1/240 s substep (Bullet stepSimulation)
@@ -648,14 +602,9 @@ __device__ __forceinline__ void substep(const ScenePar& sp, float restitution, B
     SphereHit hit;
     hit.nc = 0;
     if (!clear) sphere_hits(sp, s.x, hit);
-    if (hit.nc > 1) {
-      // the narrow phase of the general path runs at the pre-force pose / velocities, as in the oracle
-      apply_forces(s);
-      sphere_solve_many(sp, restitution, &s);
-    } else {
-      apply_forces(s);
-      if (hit.nc == 1) sphere_solve_one(hit, restitution, s.v, s.w);
-    }
+    apply_forces(s);
+    // the iterative path redoes the narrow phase in solver order; it depends on the pose only
+    if (sphere_contacts_inline(hit, restitution, s.v, s.w)) sphere_solve_iter(sp, restitution, &s);
   } else {
     Contact c[PH_MAXC];
     int nc = 0;

@@ -402,64 +402,29 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
   return qs;
 }
 
-// Sphere version for the rejuvenation kernel: the whole thread block steps in lockstep so that bodies with
-// several simultaneous contacts can be solved in compacted warps (physics.cuh, SphereCoop).  No orientation.
 #ifndef RJ_BLOCK
-#define RJ_BLOCK 256
+#define RJ_BLOCK 128
 #endif
 #ifndef RJ_MINB
-#define RJ_MINB 3  // blocks per SM the register allocation must allow
+#define RJ_MINB 6  // blocks per SM the register allocation must allow (24 warps at 80 registers)
 #endif
-template <bool TRACK_Q, bool TRAJ>
-__device__ __forceinline__ double resimulate_sphere_coop(const ScenePar& sp, const TrialPar& tp, int S, float e,
-                                                         const float* __restrict__ xt, int64_t n, int64_t i, int steps,
-                                                         Body& s, SphereCoop<RJ_BLOCK>& sh, float* traj, bool live) {
-  init_body(tp, s);
-  double qs = 0.0;
-  const float* p = xt + i;
-  float nx = p[0], ny = p[n], nz = p[2 * n];
-  for (int k = 0; k < steps; k++) {
-    const float x = nx, y = ny, z = nz;
-    if (k + 1 < steps) {
-      const float* pn = p + (int64_t)(k + 1) * 3 * n;
-      nx = pn[0]; ny = pn[n]; nz = pn[2 * n];
-    }
-    if (k >= 1) {
-      float dx = x - s.x.x, dy = y - s.x.y, dz = z - s.x.z;
-      qs += (double)(dx * dx + dy * dy + dz * dz);
-    }
-    s.x = mk3(x, y, z);
-    for (int j = 0; j < S; j++) substep_sphere_coop<RJ_BLOCK, TRACK_Q>(sp, sh, e, s);
-    if (TRAJ && live) {
-      float* o = traj + (int64_t)k * 3 * n + i;
-      o[0] = s.x.x; o[n] = s.x.y; o[2 * n] = s.x.z;
-    }
-  }
-  return qs;
-}
 
 // ---------------------------------------------------------------- K5: rejuvenation (re-simulate + MH)
 // for i = 1:N, j = 1:R: Gen.mh(trace_i, proposal, ())  (Inference/particle_filter.jl:58-62):
 //   e' ~ TruncNorm(e, 0.1, 0, 1) (proposal :17-29, Utilities/truncatednorm.jl:11-16); re-simulate steps 1..t+1
 //   with the retained x~; accept iff log u < [sum_s logN(x~_s; mu'_s) - sum_s logN(x~_s; mu_s)] - log q(e'|e)
 //   + log q(e|e').  The observation terms and the s = 1 term cancel; the PF log weight is untouched.
-// One thread per particle, the R moves of a particle form a chain and run back to back in registers.
+// One thread per particle, the R moves of a particle form a chain and run back to back in registers.  Warps are
+// independent (no shared memory, no barriers): contact response that needs no iteration is in line, the rest is
+// an out-of-line call (physics.cuh).  A sphere's orientation is not integrated here: it never feeds back.
 template <int SHAPE>
-__global__ void __launch_bounds__(SHAPE == SHAPE_SPHERE ? RJ_BLOCK : PF_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : 1)
+__global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : 1)
     k_rejuvenate(Bufs B, const Ctl* ctl, TrialPar tp, ScenePar sp, int64_t n, int64_t goff, u64 seed, int t, int S,
                  int R, double prop_sigma, u64* accept_out) {
-  __shared__ SphereCoop<SHAPE == SHAPE_SPHERE ? RJ_BLOCK : 1> sh;
-  if (SHAPE == SHAPE_SPHERE) {
-    if (threadIdx.x == 0) sh.cnt = 0;
-    __syncthreads();
-  }
   const int cur = ctl->cur ^ ctl->resampled;
-  const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  // the sphere path steps the block in lockstep: tail threads shadow the last particle and store nothing
-  const bool live = i0 < n;
-  const int64_t i = (SHAPE == SHAPE_SPHERE && !live) ? n - 1 : i0;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   unsigned int acc = 0;
-  if (SHAPE == SHAPE_SPHERE || live) {
+  if (i < n) {
     double e_old = B.e[cur][i], q_old = B.qs[cur][i];
     const double inv2s2 = 0.5 / (tp.sigma_tr * tp.sigma_tr);
     Body keep;
@@ -471,26 +436,21 @@ __global__ void __launch_bounds__(SHAPE == SHAPE_SPHERE ? RJ_BLOCK : PF_BLOCK, S
       double fwd = truncnorm_logpdf(e_new, e_old, prop_sigma, 0.0, 1.0);
       double bwd = truncnorm_logpdf(e_old, e_new, prop_sigma, 0.0, 1.0);
       Body s;
-      double q_new;
-      if (SHAPE == SHAPE_SPHERE)
-        q_new = resimulate_sphere_coop<false, false>(sp, tp, S, (float)e_new, B.xt[cur], n, i, t + 1, s,
-                                                     *reinterpret_cast<SphereCoop<RJ_BLOCK>*>(&sh), nullptr, live);
-      else
-        q_new = resimulate<SHAPE, true, false>(sp, tp, S, (float)e_new, B.xt[cur], n, i, t + 1, s, nullptr);
+      double q_new = resimulate<SHAPE, SHAPE == SHAPE_CUBE, false>(sp, tp, S, (float)e_new, B.xt[cur], n, i, t + 1, s,
+                                                                   nullptr);
       double alpha = -(q_new - q_old) * inv2s2 - fwd + bwd;
       if (log(u01(r[1])) < alpha) { e_old = e_new; q_old = q_new; keep = s; any = true; acc++; }
     }
-    if (any && live) {
+    if (any) {
       B.e[cur][i] = e_old;
       B.qs[cur][i] = q_old;
       float* st = B.st[cur];
       if (SHAPE == SHAPE_SPHERE) {
-        // orientation of a sphere is not tracked on this path (see substep); keep the stored quaternion
+        // keep the stored quaternion (see above)
         keep.q.x = st[3 * n + i]; keep.q.y = st[4 * n + i]; keep.q.z = st[5 * n + i]; keep.q.w = st[6 * n + i];
       }
       store_body(st, n, i, keep);
     }
-    if (!live) acc = 0;
   }
   if (accept_out) {
 #pragma unroll
@@ -501,29 +461,15 @@ __global__ void __launch_bounds__(SHAPE == SHAPE_SPHERE ? RJ_BLOCK : PF_BLOCK, S
 
 // ---------------------------------------------------------------- getters / stateless kernels
 template <int SHAPE>
-__global__ void __launch_bounds__(SHAPE == SHAPE_SPHERE ? RJ_BLOCK : PF_BLOCK)
+__global__ void __launch_bounds__(RJ_BLOCK)
     k_traj(const double* e, const float* xt, TrialPar tp, ScenePar sp, int64_t n, int S, int T, float* mu_out,
            double* q_out, float* state_out) {
   const int64_t i0 = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  const bool live = i0 < n;
+  if (i0 >= n) return;
   Body s;
   double qs;
-  if (SHAPE == SHAPE_SPHERE) {
-    // same block-cooperative stepping as the rejuvenation kernel (plus orientation): tail threads shadow
-    // the last particle so that the whole block reaches every barrier
-    __shared__ SphereCoop<SHAPE == SHAPE_SPHERE ? RJ_BLOCK : 1> sh;
-    if (threadIdx.x == 0) sh.cnt = 0;
-    __syncthreads();
-    const int64_t i = live ? i0 : n - 1;
-    SphereCoop<RJ_BLOCK>& shr = *reinterpret_cast<SphereCoop<RJ_BLOCK>*>(&sh);
-    if (mu_out) qs = resimulate_sphere_coop<true, true>(sp, tp, S, (float)e[i], xt, n, i, T, s, shr, mu_out, live);
-    else qs = resimulate_sphere_coop<true, false>(sp, tp, S, (float)e[i], xt, n, i, T, s, shr, nullptr, live);
-  } else {
-    if (!live) return;
-    if (mu_out) qs = resimulate<SHAPE, true, true>(sp, tp, S, (float)e[i0], xt, n, i0, T, s, mu_out);
-    else qs = resimulate<SHAPE, true, false>(sp, tp, S, (float)e[i0], xt, n, i0, T, s, nullptr);
-  }
-  if (!live) return;
+  if (mu_out) qs = resimulate<SHAPE, true, true>(sp, tp, S, (float)e[i0], xt, n, i0, T, s, mu_out);
+  else qs = resimulate<SHAPE, true, false>(sp, tp, S, (float)e[i0], xt, n, i0, T, s, nullptr);
   if (q_out) q_out[i0] = qs;
   if (state_out) store_body(state_out, n, i0, s);
 }
@@ -993,7 +939,7 @@ int smcphys_pf_rejuvenate(smcphys_handle* h, int32_t t, int32_t R, uint64_t* d_a
     LAUNCH(k_rejuvenate<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B, h->ctl, h->tp, h->sp, n,
            h->cfg.particle_offset, h->cfg.seed, t, h->cfg.substeps, R, h->cfg.proposal_sigma, acc);
   else
-    LAUNCH(k_rejuvenate<SHAPE_CUBE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B, h->ctl, h->tp, h->sp, n,
+    LAUNCH(k_rejuvenate<SHAPE_CUBE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B, h->ctl, h->tp, h->sp, n,
            h->cfg.particle_offset, h->cfg.seed, t, h->cfg.substeps, R, h->cfg.proposal_sigma, acc);
   return 0;
 }
@@ -1061,7 +1007,7 @@ int smcphys_get_particles(smcphys_handle* h, double* e, double* log_w, double* s
       LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
              h->cfg.substeps, T, d, (double*)nullptr, (float*)nullptr);
     else
-      LAUNCH(k_traj<SHAPE_CUBE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
+      LAUNCH(k_traj<SHAPE_CUBE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
              h->cfg.substeps, T, d, (double*)nullptr, (float*)nullptr);
     CK(cudaMemcpyAsync(traj, d, sizeof(float) * 3 * (size_t)T * n, cudaMemcpyDeviceToHost, h->stream));
   }
@@ -1086,7 +1032,7 @@ int smcphys_get_states(smcphys_handle* h, float* state13) {
     LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
            h->cfg.substeps, h->steps_done, (float*)nullptr, (double*)nullptr, soa);
   } else {
-    LAUNCH(k_traj<SHAPE_CUBE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
+    LAUNCH(k_traj<SHAPE_CUBE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B.e[cur], h->B.xt[cur], h->tp, h->sp, n,
            h->cfg.substeps, h->steps_done, (float*)nullptr, (double*)nullptr, soa);
   }
   LAUNCH(k_soa_to_aos, nblk(n, 256), 256, h->stream, soa, aos, n);
@@ -1296,7 +1242,7 @@ int smcphys_simulate(int32_t device, int32_t shape, int32_t S, double ceiling_ha
   if (shape == SMCPHYS_SPHERE)
     LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, st, d_ed, d_xt, tp, sp, n, S, T, d_mu, d_q, d_soa);
   else
-    LAUNCH(k_traj<SHAPE_CUBE>, nblk(n, PF_BLOCK), PF_BLOCK, st, d_ed, d_xt, tp, sp, n, S, T, d_mu, d_q, d_soa);
+    LAUNCH(k_traj<SHAPE_CUBE>, nblk(n, RJ_BLOCK), RJ_BLOCK, st, d_ed, d_xt, tp, sp, n, S, T, d_mu, d_q, d_soa);
   if (mu_out && T > 0) CK(cudaMemcpyAsync(mu_out, d_mu, sizeof(float) * 3 * (size_t)T * n, cudaMemcpyDeviceToHost, st));
   std::vector<double> q;
   if (logp_out) {
