@@ -356,15 +356,17 @@ __device__ __forceinline__ float sphere_rhs_n(const f3& n, float dist, float res
   return perr + verr;
 }
 
+// The two friction rows are written as one tangential impulse vector: with u = v + w x r the velocity of the contact
+// point and u_t its tangential part, (l1, l2) = -(u.t1, u.t2) / 3.5 clamped to the cone is J = -u_t / 3.5 clamped in
+// norm, for ANY orthonormal tangent basis - so btPlaneSpace1 is not needed, and floor, wall and edge contacts run
+// the same instructions.  v += n lambda_n + J,  w += (r x J) / I.
 __device__ __forceinline__ void sphere_solve_one(const SphereHit& hit, float restitution, f3& v, f3& w) {
-  const float inv_i = PH_INV_I_SPHERE;
   const float dinv_t = 1.0f / (PH_INV_M + PH_H * PH_H * PH_INV_I_SPHERE);  // 1 / 3.5
-  f3 t1, t2;
-  plane_space(hit.n, t1, t2);
-  const f3 r = hit.n * (-PH_H);
-  const f3 rx1 = cross3(r, t1), rx2 = cross3(r, t2);
-  const float vn = dot3(hit.n, v);
-  const float vt1 = dot3(t1, v) + dot3(rx1, w), vt2 = dot3(t2, v) + dot3(rx2, w);
+  const f3 n = hit.n;
+  const f3 r = n * (-PH_H);
+  const float vn = dot3(n, v);
+  const f3 u = v + cross3(w, r);
+  const f3 ut = u - n * dot3(n, u);
   float rest = 0.f;
   if (fabsf(vn) >= PH_REST_THRESH) rest = fmaxf(0.f, -(restitution * PH_STATIC_REST) * vn);
   const float distance = hit.dist + PH_SLOP;
@@ -373,15 +375,11 @@ __device__ __forceinline__ void sphere_solve_one(const SphereHit& hit, float res
   else perr = -distance * PH_ERP / PH_DT;
   const float ln = fmaxf(0.f, perr + verr);  // 1 / (1/m) = 1
   const float lim = PH_FRICTION * ln;
-  float l1 = -vt1 * dinv_t, l2 = -vt2 * dinv_t;
-  const float m2 = l1 * l1 + l2 * l2;
-  if (m2 > lim * lim) {
-    const float scl = lim / sqrtf(m2);
-    l1 *= scl;
-    l2 *= scl;
-  }
-  v = v + hit.n * ln + t1 * l1 + t2 * l2;
-  w = w + (rx1 * l1 + rx2 * l2) * inv_i;
+  f3 J = ut * (-dinv_t);
+  const float m2 = dot3(J, J);
+  if (m2 > lim * lim) J = J * (lim / sqrtf(m2));
+  v = v + n * ln + J;
+  w = w + cross3(r, J) * PH_INV_I_SPHERE;
 }
 
 // Contact response that needs no iteration, in line: one contact (closed form above), and the two-contact cases
@@ -551,15 +549,20 @@ __device__ __noinline__ void sphere_solve_generic(const f3* n, const float* dist
 
 // Contacts that do need the iterative solver (10-15 % of the two-contact substeps of a filter run, and every
 // corner): out of line, so that the registers of the hot loop are sized by the free-flight / single-contact path.
-__device__ __noinline__ void sphere_solve_iter(ScenePar sp, float restitution, Body* s) {
+// Everything travels by value: taking the address of the caller's Body would pin it to local memory.
+struct VelPair { f3 v, w; };
+__device__ __noinline__ VelPair sphere_solve_iter(float ceil_half, float restitution, f3 x, f3 v, f3 w) {
+  ScenePar sp;
+  sp.ceil_half = ceil_half;
   f3 n[4];
   float dist[4];
-  const int nc = sphere_contacts_ordered(sp, s->x, n, dist);
-  f3 v = s->v, w = s->w;
+  const int nc = sphere_contacts_ordered(sp, x, n, dist);
   if (nc == 2) sphere_solve_two(n, dist, restitution, v, w);
   else if (nc > 0) sphere_solve_generic(n, dist, nc, restitution, &v, &w);
-  s->v = v;
-  s->w = w;
+  VelPair r;
+  r.v = v;
+  r.w = w;
+  return r;
 }
 
 // ---------------------------------------------------------------- one 1/240 s substep (Bullet stepSimulation)
@@ -604,7 +607,11 @@ __device__ __forceinline__ void substep(const ScenePar& sp, float restitution, B
     if (!clear) sphere_hits(sp, s.x, hit);
     apply_forces(s);
     // the iterative path redoes the narrow phase in solver order; it depends on the pose only
-    if (sphere_contacts_inline(hit, restitution, s.v, s.w)) sphere_solve_iter(sp, restitution, &s);
+    if (sphere_contacts_inline(hit, restitution, s.v, s.w)) {
+      const VelPair r = sphere_solve_iter(sp.ceil_half, restitution, s.x, s.v, s.w);
+      s.v = r.v;
+      s.w = r.w;
+    }
   } else {
     Contact c[PH_MAXC];
     int nc = 0;

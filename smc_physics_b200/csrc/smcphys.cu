@@ -406,7 +406,7 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
 #define RJ_BLOCK 128
 #endif
 #ifndef RJ_MINB
-#define RJ_MINB 6  // blocks per SM the register allocation must allow (24 warps at 80 registers)
+#define RJ_MINB 8  // blocks per SM the register allocation must allow (32 warps at 64 registers)
 #endif
 
 // ---------------------------------------------------------------- K5: rejuvenation (re-simulate + MH)
@@ -427,29 +427,34 @@ __global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : 1)
   if (i < n) {
     double e_old = B.e[cur][i], q_old = B.qs[cur][i];
     const double inv2s2 = 0.5 / (tp.sigma_tr * tp.sigma_tr);
-    Body keep;
-    bool any = false;
+    float* st = B.st[cur];
     for (int j = 0; j < R; j++) {
       uint32_t r[4];
       philox4x32_10(seed, (uint32_t)(goff + i), (uint32_t)t, (uint32_t)j, (uint32_t)ST_PROPOSAL, r);
-      double e_new = truncnorm_sample(u01(r[0]), e_old, prop_sigma, 0.0, 1.0);
-      double fwd = truncnorm_logpdf(e_new, e_old, prop_sigma, 0.0, 1.0);
-      double bwd = truncnorm_logpdf(e_old, e_new, prop_sigma, 0.0, 1.0);
+      const double e_new = truncnorm_sample(u01(r[0]), e_old, prop_sigma, 0.0, 1.0);
+      const double fwd = truncnorm_logpdf(e_new, e_old, prop_sigma, 0.0, 1.0);
+      const double bwd = truncnorm_logpdf(e_old, e_new, prop_sigma, 0.0, 1.0);
+      const double log_u = log(u01(r[1]));
       Body s;
-      double q_new = resimulate<SHAPE, SHAPE == SHAPE_CUBE, false>(sp, tp, S, (float)e_new, B.xt[cur], n, i, t + 1, s,
-                                                                   nullptr);
-      double alpha = -(q_new - q_old) * inv2s2 - fwd + bwd;
-      if (log(u01(r[1])) < alpha) { e_old = e_new; q_old = q_new; keep = s; any = true; acc++; }
+      const double q_new = resimulate<SHAPE, SHAPE == SHAPE_CUBE, false>(sp, tp, S, (float)e_new, B.xt[cur], n, i, t + 1,
+                                                                         s, nullptr);
+      const double alpha = -(q_new - q_old) * inv2s2 - fwd + bwd;
+      if (log_u < alpha) {
+        // accepted: the simulator state goes out right away, so nothing but (e, q) stays live across the moves
+        e_old = e_new;
+        q_old = q_new;
+        acc++;
+        st[0 * n + i] = s.x.x; st[1 * n + i] = s.x.y; st[2 * n + i] = s.x.z;
+        if (SHAPE == SHAPE_CUBE) {  // a sphere keeps its stored quaternion (see above)
+          st[3 * n + i] = s.q.x; st[4 * n + i] = s.q.y; st[5 * n + i] = s.q.z; st[6 * n + i] = s.q.w;
+        }
+        st[7 * n + i] = s.v.x; st[8 * n + i] = s.v.y; st[9 * n + i] = s.v.z;
+        st[10 * n + i] = s.w.x; st[11 * n + i] = s.w.y; st[12 * n + i] = s.w.z;
+      }
     }
-    if (any) {
+    if (acc) {
       B.e[cur][i] = e_old;
       B.qs[cur][i] = q_old;
-      float* st = B.st[cur];
-      if (SHAPE == SHAPE_SPHERE) {
-        // keep the stored quaternion (see above)
-        keep.q.x = st[3 * n + i]; keep.q.y = st[4 * n + i]; keep.q.z = st[5 * n + i]; keep.q.w = st[6 * n + i];
-      }
-      store_body(st, n, i, keep);
     }
   }
   if (accept_out) {
