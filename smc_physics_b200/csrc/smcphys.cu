@@ -402,6 +402,27 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
   return qs;
 }
 
+// The sphere chain of the rejuvenation kernel as a call: inside, the register allocation sees nothing but the
+// chain (body, elasticity, the prefetched row), while the Metropolis-Hastings state of the caller (five doubles,
+// counters, pointers) is parked by the calling convention once per chain instead of being spilled in the substep loop.
+struct ChainOut {
+  double qs;
+  f3 x, v, w;
+};
+__device__ __noinline__ ChainOut resimulate_sphere_call(float ceil_half, f3 x0, f3 v0, int S, float e,
+                                                        const float* __restrict__ xt, int64_t n, int64_t i, int steps) {
+  ScenePar sp;
+  sp.ceil_half = ceil_half;
+  TrialPar tp;
+  tp.x0[0] = x0.x; tp.x0[1] = x0.y; tp.x0[2] = x0.z;
+  tp.v0[0] = v0.x; tp.v0[1] = v0.y; tp.v0[2] = v0.z;
+  Body s;
+  ChainOut o;
+  o.qs = resimulate<SHAPE_SPHERE, false, false>(sp, tp, S, e, xt, n, i, steps, s, nullptr);
+  o.x = s.x; o.v = s.v; o.w = s.w;
+  return o;
+}
+
 #ifndef RJ_BLOCK
 #define RJ_BLOCK 128
 #endif
@@ -428,6 +449,7 @@ __global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : 1)
     double e_old = B.e[cur][i], q_old = B.qs[cur][i];
     const double inv2s2 = 0.5 / (tp.sigma_tr * tp.sigma_tr);
     float* st = B.st[cur];
+    const float* xt_cur = B.xt[cur];
     for (int j = 0; j < R; j++) {
       uint32_t r[4];
       philox4x32_10(seed, (uint32_t)(goff + i), (uint32_t)t, (uint32_t)j, (uint32_t)ST_PROPOSAL, r);
@@ -436,8 +458,15 @@ __global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : 1)
       const double bwd = truncnorm_logpdf(e_old, e_new, prop_sigma, 0.0, 1.0);
       const double log_u = log(u01(r[1]));
       Body s;
-      const double q_new = resimulate<SHAPE, SHAPE == SHAPE_CUBE, false>(sp, tp, S, (float)e_new, B.xt[cur], n, i, t + 1,
-                                                                         s, nullptr);
+      double q_new;
+      if (SHAPE == SHAPE_SPHERE) {
+        const ChainOut o = resimulate_sphere_call(sp.ceil_half, mk3(tp.x0[0], tp.x0[1], tp.x0[2]),
+                                                  mk3(tp.v0[0], tp.v0[1], tp.v0[2]), S, (float)e_new, xt_cur, n, i, t + 1);
+        q_new = o.qs;
+        s.x = o.x; s.v = o.v; s.w = o.w;
+      } else {
+        q_new = resimulate<SHAPE, true, false>(sp, tp, S, (float)e_new, xt_cur, n, i, t + 1, s, nullptr);
+      }
       const double alpha = -(q_new - q_old) * inv2s2 - fwd + bwd;
       if (log_u < alpha) {
         // accepted: the simulator state goes out right away, so nothing but (e, q) stays live across the moves
