@@ -600,19 +600,19 @@ __device__ __forceinline__ void integrate_q(Body& s) {
 template <int SHAPE, bool TRACK_Q>
 __device__ __forceinline__ void substep(const ScenePar& sp, float restitution, Body& s, Manifold& pm) {
   const float dt = PH_DT;
-  const bool clear = body_clear<SHAPE>(s.x, sp.ceil_half);
   if (SHAPE == SHAPE_SPHERE) {
+    // sphere_hits starts with the same four range tests a clear-region test would make
     SphereHit hit;
-    hit.nc = 0;
-    if (!clear) sphere_hits(sp, s.x, hit);
+    sphere_hits(sp, s.x, hit);
     apply_forces(s);
     // the iterative path redoes the narrow phase in solver order; it depends on the pose only
-    if (sphere_contacts_inline(hit, restitution, s.v, s.w)) {
+    if (hit.nc > 0 && sphere_contacts_inline(hit, restitution, s.v, s.w)) {
       const VelPair r = sphere_solve_iter(sp.ceil_half, restitution, s.x, s.v, s.w);
       s.v = r.v;
       s.w = r.w;
     }
   } else {
+    const bool clear = body_clear<SHAPE>(s.x, sp.ceil_half);
     Contact c[PH_MAXC];
     int nc = 0;
     if (!clear) nc = collide_cube(sp, s, pm, c);

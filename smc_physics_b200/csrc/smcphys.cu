@@ -354,18 +354,26 @@ __global__ void k_gather(Bufs B, const Ctl* ctl, int64_t n) {
 #pragma unroll
   for (int c = 0; c < 13; c++) B.st[nxt][c * n + k] = B.st[cur][c * n + a];
 }
-// history rows 0..t: blockIdx.y = s
-__global__ void k_gather_hist(Bufs B, const Ctl* ctl, int64_t n) {
+// history rows 0..t.  Systematic resampling keeps the ancestors sorted, so a warp reads (almost) consecutive
+// addresses; each thread moves GH_ROWS x 3 floats of one particle with all loads in flight before the first store,
+// and reads its ancestor index once per GH_ROWS rows.  blockIdx.y = group of GH_ROWS rows.
+#define GH_ROWS 8
+__global__ void __launch_bounds__(256) k_gather_hist(Bufs B, const Ctl* ctl, int64_t n, int rows) {
   if (!ctl->resampled) return;
   const int cur = ctl->cur, nxt = cur ^ 1;
-  int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (k >= n) return;
-  int64_t a = B.idx[k];
-  int64_t row = (int64_t)blockIdx.y * 3;
-  const float* src = B.xt[cur];
-  float* dst = B.xt[nxt];
+  const int64_t a = B.idx[k];
+  const int c0 = (int)blockIdx.y * (GH_ROWS * 3), c1 = rows * 3;
+  const float* __restrict__ src = B.xt[cur] + (int64_t)c0 * n + a;
+  float* __restrict__ dst = B.xt[nxt] + (int64_t)c0 * n + k;
+  float v[GH_ROWS * 3];
 #pragma unroll
-  for (int c = 0; c < 3; c++) dst[(row + c) * n + k] = src[(row + c) * n + a];
+  for (int c = 0; c < GH_ROWS * 3; c++)
+    if (c0 + c < c1) v[c] = __ldg(src + (int64_t)c * n);
+#pragma unroll
+  for (int c = 0; c < GH_ROWS * 3; c++)
+    if (c0 + c < c1) __stcs(dst + (int64_t)c * n, v[c]);
 }
 
 // ---------------------------------------------------------------- re-simulation from t = 0
@@ -957,7 +965,7 @@ int smcphys_pf_resample_local(smcphys_handle* h, int32_t t) {
   }
   ProfScope ps(h, SMCPHYS_K_GATHER);
   LAUNCH(k_gather, nblk(n, 256), 256, h->stream, h->B, h->ctl, n);
-  LAUNCH(k_gather_hist, dim3(nblk(n, 256), (unsigned)(t + 1)), 256, h->stream, h->B, h->ctl, n);
+  LAUNCH(k_gather_hist, dim3(nblk(n, 256), (unsigned)((t + GH_ROWS) / GH_ROWS)), 256, h->stream, h->B, h->ctl, n, t + 1);
   return 0;
 }
 
