@@ -271,6 +271,15 @@ def gpu_arm(args):
     except OSError:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
+    # measured DRAM traffic of the mean k_rejuvenate launch, from the committed ncu capture of this same workload
+    traffic = None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_rejuvenate"]
+        c = tr["config"]
+        if (c["shape"], c["particles"], c["timesteps"], c["moves"], c["substeps"]) == (args.shape, n, T, R, S):
+            traffic = tr["dram_bytes"]
+    except (OSError, ValueError, KeyError):
+        pass
     res_steps = [t for t, s in enumerate(stats or []) if s["resampled"]]
     gather_bytes = sum(n * (2 * (68 + 12 * (t + 1)) + 12) for t in res_steps) * args.steps
     g_ms = ktime[sp.K_GATHER][0]
@@ -284,7 +293,9 @@ def gpu_arm(args):
                 "ms_per_step": e2e_s * 1e3},
         "gpu_launches": int(launches),
         "roofline": {"kernel": "k_rejuvenate", "bound": "fp32", "achieved": rej_tf, "peak": peak_tf, "unit": "TFLOP/s",
-                     "frac": rej_tf / peak_tf if peak_tf else None, "traffic": None,
+                     "frac": rej_tf / peak_tf if peak_tf else None, "traffic": traffic,
+                     "traffic_note": "dram__bytes_read+write of the t=60 launch (ncu --set full, profiles/); algorithmic "
+                                     "bytes of that launch = R*12*(t+1)*n = %.3g" % (R * 12 * 61 * n),
                      "peak_source": "FP32 FMA probe run in this process (smcphys_fp32_peak); not in MEASURED_PEAKS.json",
                      "launches": int(rej_groups), "avg_launch_ms": rej_ms / max(rej_groups, 1),
                      "flop_per_launch_avg": flop_run / T, "share_of_step": shares,
