@@ -111,8 +111,15 @@ int64_t smcphys_pf_payload_words(smcphys_handle* h, int32_t t);
  * (slots_per_rank = N / G), each chunk SoA [word][count]. */
 int smcphys_pf_pack(smcphys_handle* h, int32_t t, const double* d_global_max, uint64_t W_before, uint64_t W_total,
                     double u0, int64_t k_lo, int64_t k_hi, int64_t slots_per_rank, float* d_send);
+/* The part of this shard's offspring that stays on this shard - global slots [k_lo, k_hi), a sub-range of both its
+ * offspring range and its own slot range - gathered straight into the local slots slot0.. (= k_lo - particle_offset)
+ * of the idle buffer, without a trip through the send / receive buffers.  Call before pf_unpack of the same step;
+ * pf_pack then only handles the ranges that leave the shard. */
+int smcphys_pf_gather_local(smcphys_handle* h, int32_t t, const double* d_global_max, uint64_t W_before,
+                            uint64_t W_total, double u0, int64_t k_lo, int64_t k_hi, int64_t slot0);
 /* unpack n_chunks received chunks: chunk c holds counts[c] particles for local slots starting at slot0[c],
- * at word offset word_off[c] of d_recv (host arrays).  Resets log weights to 0 and switches buffers. */
+ * at word offset word_off[c] of d_recv (host arrays).  Together with pf_gather_local the chunks must fill every
+ * local slot exactly once.  Resets log weights to 0 and switches buffers. */
 int smcphys_pf_unpack(smcphys_handle* h, int32_t t, const float* d_recv, int32_t n_chunks, const int64_t* counts,
                       const int64_t* slot0, const int64_t* word_off);
 /* single-shard resampling step with the decision taken on the device (no host synchronisation) */

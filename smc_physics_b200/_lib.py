@@ -60,6 +60,8 @@ SIGNATURES = {
     "smcphys_pf_payload_words": (C.c_int64, [_H, C.c_int32]),
     "smcphys_pf_pack": (C.c_int, [_H, C.c_int32, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double, C.c_int64, C.c_int64,
                                   C.c_int64, C.c_void_p]),
+    "smcphys_pf_gather_local": (C.c_int, [_H, C.c_int32, C.c_void_p, C.c_uint64, C.c_uint64, C.c_double, C.c_int64,
+                                          C.c_int64, C.c_int64]),
     "smcphys_pf_unpack": (C.c_int, [_H, C.c_int32, C.c_void_p, C.c_int32, _ip, _ip, _ip]),
     "smcphys_pf_resample_local": (C.c_int, [_H, C.c_int32]),
     "smcphys_pf_rejuvenate": (C.c_int, [_H, C.c_int32, C.c_int32, C.c_void_p]),

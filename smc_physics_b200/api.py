@@ -184,6 +184,10 @@ class ParticleFilter:
         check(lib().smcphys_pf_pack(self._h, t, C.c_void_p(d_global_max), W_before, W_total, u0, k_lo, k_hi,
                                     slots_per_rank, C.c_void_p(d_send)))
 
+    def pf_gather_local(self, t, d_global_max, W_before, W_total, u0, k_lo, k_hi, slot0):
+        check(lib().smcphys_pf_gather_local(self._h, t, C.c_void_p(d_global_max), W_before, W_total, u0, k_lo, k_hi,
+                                            slot0))
+
     def pf_unpack(self, t, d_recv, counts, slot0, word_off):
         c = np.ascontiguousarray(counts, dtype=np.int64)
         s = np.ascontiguousarray(slot0, dtype=np.int64)

@@ -342,12 +342,14 @@ __global__ void k_index(Bufs B, const Ctl* ctl, int64_t n, int64_t Nglob, u64 U0
 
 // ---------------------------------------------------------------- K4: gather offspring
 // traces := traces[parents]; log weights := 0 (Gen.maybe_resample!, particle_filter.jl:55).
-__global__ void k_gather(Bufs B, const Ctl* ctl, int64_t n) {
-  if (!ctl->resampled) return;
+// Offspring j = 0..count-1 (ancestor idx[j]) go to the local slots slot0 + j.  gate != 0: skip unless the device-side
+// decision of this step says "resample" (single shard); the sharded filter decides on the host and passes 0.
+__global__ void k_gather(Bufs B, const Ctl* ctl, int64_t n, int64_t count, int64_t slot0, int gate) {
+  if (gate && !ctl->resampled) return;
   const int cur = ctl->cur, nxt = cur ^ 1;
-  int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= n) return;
-  int64_t a = B.idx[k];
+  int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= count) return;
+  const int64_t a = B.idx[j], k = slot0 + j;
   B.e[nxt][k] = B.e[cur][a];
   B.qs[nxt][k] = B.qs[cur][a];
   B.logw[k] = 0.0;
@@ -358,12 +360,13 @@ __global__ void k_gather(Bufs B, const Ctl* ctl, int64_t n) {
 // addresses; each thread moves GH_ROWS x 3 floats of one particle with all loads in flight before the first store,
 // and reads its ancestor index once per GH_ROWS rows.  blockIdx.y = group of GH_ROWS rows.
 #define GH_ROWS 8
-__global__ void __launch_bounds__(256) k_gather_hist(Bufs B, const Ctl* ctl, int64_t n, int rows) {
-  if (!ctl->resampled) return;
+__global__ void __launch_bounds__(256) k_gather_hist(Bufs B, const Ctl* ctl, int64_t n, int rows, int64_t count,
+                                                     int64_t slot0, int gate) {
+  if (gate && !ctl->resampled) return;
   const int cur = ctl->cur, nxt = cur ^ 1;
-  const int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (k >= n) return;
-  const int64_t a = B.idx[k];
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= count) return;
+  const int64_t a = B.idx[j], k = slot0 + j;
   const int c0 = (int)blockIdx.y * (GH_ROWS * 3), c1 = rows * 3;
   const float* __restrict__ src = B.xt[cur] + (int64_t)c0 * n + a;
   float* __restrict__ dst = B.xt[nxt] + (int64_t)c0 * n + k;
@@ -700,6 +703,7 @@ struct smcphys_handle {
   bool trial_set = false;
   int steps_done = -1;  // PF steps applied to the particles; -1 = not initialised
   int ntiles = 0;
+  int64_t local_gathered = 0;  // slots of the current resampling step already filled by pf_gather_local
   std::vector<void*> allocs;
   bool prof = false;
   struct Ev { int cls; cudaEvent_t a, b; };
@@ -964,8 +968,9 @@ int smcphys_pf_resample_local(smcphys_handle* h, int32_t t) {
     LAUNCH(k_index, nblk(n, 256), 256, h->stream, h->B, h->ctl, n, n, (u64)r[0], &h->ctl->W, (u64)0, (int64_t)0, n, 1);
   }
   ProfScope ps(h, SMCPHYS_K_GATHER);
-  LAUNCH(k_gather, nblk(n, 256), 256, h->stream, h->B, h->ctl, n);
-  LAUNCH(k_gather_hist, dim3(nblk(n, 256), (unsigned)((t + GH_ROWS) / GH_ROWS)), 256, h->stream, h->B, h->ctl, n, t + 1);
+  LAUNCH(k_gather, nblk(n, 256), 256, h->stream, h->B, h->ctl, n, n, (int64_t)0, 1);
+  LAUNCH(k_gather_hist, dim3(nblk(n, 256), (unsigned)((t + GH_ROWS) / GH_ROWS)), 256, h->stream, h->B, h->ctl, n, t + 1,
+         n, (int64_t)0, 1);
   return 0;
 }
 
@@ -1184,6 +1189,25 @@ int smcphys_pf_pack(smcphys_handle* h, int32_t t, const double* d_global_max, ui
   return 0;
 }
 
+int smcphys_pf_gather_local(smcphys_handle* h, int32_t t, const double* d_global_max, uint64_t W_before,
+                            uint64_t W_total, double u0, int64_t k_lo, int64_t k_hi, int64_t slot0) {
+  NEED_TRIAL(h);
+  if (t != h->steps_done - 1) return fail(SMCPHYS_ESTATE, "pf_gather_local: t is not the current step");
+  const int64_t n = h->cfg.num_particles, count = k_hi - k_lo;
+  if (!d_global_max || count < 0 || slot0 < 0 || slot0 + count > n)
+    return fail(SMCPHYS_EINVAL, "pf_gather_local: bad arguments");
+  h->local_gathered = count;
+  if (count == 0) return 0;
+  u64 U0 = (u64)(u0 * 4294967296.0);
+  ProfScope ps(h, SMCPHYS_K_GATHER);
+  LAUNCH(k_cdf, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, d_global_max, n, (u64)W_before, 0);
+  LAUNCH(k_index, nblk(count, 256), 256, h->stream, h->B, h->ctl, n, h->cfg.global_particles, U0, (const u64*)nullptr,
+         (u64)W_total, k_lo, count, 0);
+  LAUNCH(k_gather, nblk(count, 256), 256, h->stream, h->B, h->ctl, n, count, slot0, 0);
+  LAUNCH(k_gather_hist, dim3(nblk(count, 256), (unsigned)((t + GH_ROWS) / GH_ROWS)), 256, h->stream, h->B, h->ctl, n,
+         t + 1, count, slot0, 0);
+  return 0;
+}
 int smcphys_pf_unpack(smcphys_handle* h, int32_t t, const float* d_recv, int32_t n_chunks, const int64_t* counts,
                       const int64_t* slot0, const int64_t* word_off) {
   NEED_TRIAL(h);
@@ -1197,7 +1221,9 @@ int smcphys_pf_unpack(smcphys_handle* h, int32_t t, const float* d_recv, int32_t
       return fail(SMCPHYS_EINVAL, "pf_unpack: chunk outside the shard");
     total += counts[c];
   }
-  if (total != n) return fail(SMCPHYS_EINVAL, "pf_unpack: chunks must fill every local slot exactly once");
+  if (total + h->local_gathered != n)
+    return fail(SMCPHYS_EINVAL, "pf_unpack: chunks (+ pf_gather_local) must fill every local slot exactly once");
+  h->local_gathered = 0;
   ProfScope ps(h, SMCPHYS_K_GATHER);
   for (int c = 0; c < n_chunks; c++) {
     if (counts[c] == 0) continue;

@@ -71,6 +71,9 @@ class _CudaShard:
     def pack(self, t, global_max, W_before, W_total, u0, k_lo, k_hi, spr, send):
         self.pf.pf_pack(t, global_max.data_ptr(), W_before, W_total, u0, k_lo, k_hi, spr, send.data_ptr())
 
+    def gather_local(self, t, global_max, W_before, W_total, u0, k_lo, k_hi, slot0):
+        self.pf.pf_gather_local(t, global_max.data_ptr(), W_before, W_total, u0, k_lo, k_hi, slot0)
+
     def unpack(self, t, recv, counts, slot0, word_off):
         self.pf.pf_unpack(t, recv.data_ptr(), counts, slot0, word_off)
 
@@ -153,17 +156,30 @@ class ShardedFilter:
             send, recv, slot0 = plan_migration(ranges, self.n, self.rank)
             words = sh.payload_words(t)
             k_lo, k_hi = ranges[self.rank]
-            sbuf = torch.empty(max(1, (k_hi - k_lo) * words), dtype=torch.float32, device=self.dev)
-            rbuf = torch.empty(self.n * words, dtype=torch.float32, device=self.dev)
-            sh.pack(t, self._max, sum(W_all[:self.rank]), W_total, u0, k_lo, k_hi, self.n, sbuf)
-            if G > 1:
-                dist.all_to_all_single(rbuf, sbuf[:(k_hi - k_lo) * words], [c * words for c in recv],
-                                       [c * words for c in send], group=self.group)
+            W_before = sum(W_all[:self.rank])
+            my_lo, my_hi = self.rank * self.n, (self.rank + 1) * self.n
+            # offspring that stay on this rank (the bulk: resampling preserves order) are gathered in place ...
+            l_lo, l_hi = max(k_lo, my_lo), min(k_hi, my_hi)
+            if l_hi > l_lo:
+                sh.gather_local(t, self._max, W_before, W_total, u0, l_lo, l_hi, l_lo - my_lo)
             else:
-                rbuf = sbuf
+                sh.gather_local(t, self._max, W_before, W_total, u0, my_lo, my_lo, 0)
+            # ... and only the ranges below / above the own slots travel: chunks for ranks < rank, then ranks > rank
+            send[self.rank] = recv[self.rank] = 0
+            below, above = (k_lo, min(k_hi, my_lo)), (max(k_lo, my_hi), k_hi)
+            n_below = max(0, below[1] - below[0])
+            sbuf = torch.empty(max(1, sum(send) * words), dtype=torch.float32, device=self.dev)
+            rbuf = torch.empty(max(1, sum(recv) * words), dtype=torch.float32, device=self.dev)
+            if n_below > 0:
+                sh.pack(t, self._max, W_before, W_total, u0, below[0], below[1], self.n, sbuf)
+            if above[1] > above[0]:
+                sh.pack(t, self._max, W_before, W_total, u0, above[0], above[1], self.n, sbuf[n_below * words:])
+            if G > 1:
+                dist.all_to_all_single(rbuf[:sum(recv) * words], sbuf[:sum(send) * words], [c * words for c in recv],
+                                       [c * words for c in send], group=self.group)
             word_off = np.concatenate([[0], np.cumsum([c * words for c in recv])[:-1]]).astype(np.int64)
             sh.unpack(t, rbuf, recv, slot0, word_off)
-            self.migrated_particles += self.n - recv[self.rank]
+            self.migrated_particles += sum(recv)
         if R > 0:
             sh.rejuvenate(t, R)
 
@@ -256,6 +272,14 @@ class LocalShards:
             self._sync()
             for d in range(G):
                 send_d, recv, slot0 = plans[d]
+                recv = list(recv)
+                # the chunk that stays on shard d is gathered in place (as ShardedFilter does); the rest is copied
+                l_lo, l_hi = max(ranges[d][0], d * self.n), min(ranges[d][1], (d + 1) * self.n)
+                if l_hi <= l_lo:
+                    l_lo = l_hi = d * self.n
+                self.pfs[d].pf_gather_local(t, self._max[d].data_ptr(), sum(W_all[:d]), W_total, u0, l_lo, l_hi,
+                                            l_lo - d * self.n)
+                recv[d] = 0
                 rb = torch.empty(self.n * words, dtype=torch.float32, device=self.devs[d])
                 off = 0
                 word_off = []

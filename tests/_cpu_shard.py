@@ -1,7 +1,7 @@
 """TEST INFRASTRUCTURE: a CPU stand-in for one shard of the sharded filter.
 
 It implements the shard interface smc_physics_b200.sharded.ShardedFilter drives (init / extend / weight_sums /
-payload_words / pack / unpack / rejuvenate) with numpy and the oracle's integer weight arithmetic, so that the
+payload_words / gather_local / pack / unpack / rejuvenate) with numpy and the oracle's integer weight arithmetic, so that the
 host logic of the N > 1 path (decision, offspring ranges, chunk planning, the exchanges) runs on CPU over gloo.
 The "physics" is a synthetic, deterministic log-likelihood; the payload of a particle is (identity, elasticity,
 steps survived).  Never imported by the product.
@@ -46,12 +46,31 @@ class CpuShard:
     def payload_words(self, t):
         return self.WORDS
 
-    def pack(self, t, global_max, W_before, W_total, u0, k_lo, k_hi, spr, send):
+    def _ancestors(self, W_before, W_total, u0, k_lo, k_hi):
         cdf = np.cumsum(self.q, dtype=np.uint64) + np.uint64(W_before)
         U0 = int(u0 * 4294967296.0)
-        ks = range(k_lo, k_hi)
-        tau = np.array([orc.lib().oracle_sys_threshold(U0, k, W_total, self.N) for k in ks], dtype=np.uint64)
-        anc = np.minimum(np.searchsorted(cdf, tau, side="right"), self.n - 1)
+        tau = np.array([orc.lib().oracle_sys_threshold(U0, k, W_total, self.N) for k in range(k_lo, k_hi)],
+                       dtype=np.uint64)
+        return np.minimum(np.searchsorted(cdf, tau, side="right"), self.n - 1)
+
+    def _next(self):
+        if getattr(self, "_nxt", None) is None:
+            self._nxt = (np.empty_like(self.ident), np.empty_like(self.e), np.empty_like(self.age))
+            self._filled = 0
+        return self._nxt
+
+    def gather_local(self, t, global_max, W_before, W_total, u0, k_lo, k_hi, slot0):
+        """offspring [k_lo, k_hi) that stay on this shard go straight to the local slots slot0.."""
+        nxt = self._next()
+        cnt = k_hi - k_lo
+        if cnt > 0:
+            anc = self._ancestors(W_before, W_total, u0, k_lo, k_hi)
+            for dst, f in zip(nxt, (self.ident, self.e, self.age)):
+                dst[slot0:slot0 + cnt] = f[anc]
+        self._filled += cnt
+
+    def pack(self, t, global_max, W_before, W_total, u0, k_lo, k_hi, spr, send):
+        anc = self._ancestors(W_before, W_total, u0, k_lo, k_hi)
         out = send.numpy()
         fields = (self.ident, self.e, self.age)
         pos = 0
@@ -67,14 +86,17 @@ class CpuShard:
 
     def unpack(self, t, recv, counts, slot0, word_off):
         buf = recv.numpy()
-        ident, e, age = np.empty_like(self.ident), np.empty_like(self.e), np.empty_like(self.age)
+        ident, e, age = self._next()
         for c, s0, wo in zip(counts, slot0, word_off):
             if c == 0:
                 continue
             ident[s0:s0 + c] = buf[wo:wo + c]
             e[s0:s0 + c] = buf[wo + c:wo + 2 * c]
             age[s0:s0 + c] = buf[wo + 2 * c:wo + 3 * c]
+            self._filled += c
+        assert self._filled == self.n, "gather_local + unpack must fill every local slot exactly once"
         self.ident, self.e, self.age = ident, e, age
+        self._nxt = None
         self.lw = np.zeros(self.n)
 
     def rejuvenate(self, t, R):
