@@ -157,6 +157,7 @@ __device__ __forceinline__ int collide_cube(const ScenePar& sp, const Body& s, M
     }
     for (int i = 0; i < pm.n; i++) { out[nc].r = wa[i] - s.x; out[nc].n = mk3(0.f, 0.f, 1.f); out[nc].dist = dist[i]; nc++; }
   }
+#pragma unroll 1
   for (int b = 0; b < 5; b++) {
     f3 c, bh;
     static_box(b, sp.ceil_half, c, bh);
@@ -284,6 +285,103 @@ __device__ __forceinline__ void solve_contacts(const Contact* c, int nc, float r
   }
   v = v + dv;
   w = w + dw;
+}
+
+// ---------------------------------------------------------------- cube: plane-manifold contacts in registers
+// The cube's most common contact set is 1-4 points of the persistent plane manifold and nothing else (resting or
+// tumbling on the floor away from the walls).  All of them share n = +z, t1 = (0,-1,0), t2 = (1,0,0) (btPlaneSpace1
+// of +z), so a row is its arm r alone: r x n = (r.y, -r.x, 0), r x t1 = (r.z, 0, -r.x), r x t2 = (0, r.z, -r.y).
+// Same rows, same sweep order, same exit rule as solve_contacts - the terms multiplied by the zero components of
+// n, t1, t2 are simply not computed - with every row in registers (the general solver indexes 8 x 3 rows of
+// 9 floats in local memory).  Loops are unrolled over the four manifold slots and predicated on nc.
+struct VelPair { f3 v, w; };
+__device__ __noinline__ VelPair solve_plane_contacts(const Contact* c, int nc, float restitution, f3 v, f3 w) {
+  const float inv_m = PH_INV_M, inv_i = PH_INV_I_CUBE;
+  const float crest = restitution * PH_STATIC_REST;
+  f3 r[4];
+  float den[4][3], dinv[4][3], rhs[4][3], app[4][3];
+#pragma unroll
+  for (int i = 0; i < 4; i++) {
+    if (i < nc) {
+      r[i] = c[i].r;
+      const float rx2 = r[i].x * r[i].x, ry2 = r[i].y * r[i].y, rz2 = r[i].z * r[i].z;
+      den[i][0] = inv_m + (ry2 + rx2) * inv_i;
+      den[i][1] = inv_m + (rz2 + rx2) * inv_i;
+      den[i][2] = inv_m + (rz2 + ry2) * inv_i;
+      const float relv0 = v.z + (r[i].y * w.x - r[i].x * w.y);
+      const float relv1 = -v.y + (r[i].z * w.x - r[i].x * w.z);
+      const float relv2 = v.x + (r[i].z * w.y - r[i].y * w.z);
+      float rest = 0.f;
+      if (fabsf(relv0) >= PH_REST_THRESH) rest = fmaxf(0.f, -crest * relv0);
+      const float distance = c[i].dist + PH_SLOP;
+      float verr = rest - relv0, perr = 0.f;
+      if (distance > 0.f) verr -= distance / PH_DT;
+      else perr = -distance * PH_ERP / PH_DT;
+#pragma unroll
+      for (int k = 0; k < 3; k++) { dinv[i][k] = 1.0f / den[i][k]; app[i][k] = 0.f; }
+      rhs[i][0] = (perr + verr) * dinv[i][0];
+      rhs[i][1] = -relv1 * dinv[i][1];
+      rhs[i][2] = -relv2 * dinv[i][2];
+    }
+  }
+  f3 dv = mk3(0.f, 0.f, 0.f), dw = mk3(0.f, 0.f, 0.f);
+  for (int it = 0; it < PH_ITERS; it++) {
+    float resid = 0.f;
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      if (i < nc) {
+        float dimp = rhs[i][0] - (dv.z + (r[i].y * dw.x - r[i].x * dw.y)) * dinv[i][0];
+        const float sum = app[i][0] + dimp;
+        if (sum < 0.f) { dimp = -app[i][0]; app[i][0] = 0.f; }
+        else app[i][0] = sum;
+        dv.z += dimp * inv_m;
+        const float q = dimp * inv_i;
+        dw.x += r[i].y * q;
+        dw.y -= r[i].x * q;
+        const float dvel = dimp * den[i][0];
+        resid = fmaxf(resid, dvel * dvel);
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < 4; i++) {
+      if (i < nc) {
+        const float lim = PH_FRICTION * app[i][0];
+        float s1 = app[i][1] + (rhs[i][1] - (-dv.y + (r[i].z * dw.x - r[i].x * dw.z)) * dinv[i][1]);
+        float s2 = app[i][2] + (rhs[i][2] - (dv.x + (r[i].z * dw.y - r[i].y * dw.z)) * dinv[i][2]);
+        const float l2 = s1 * s1 + s2 * s2;
+        if (l2 > lim * lim) {
+          const float scl = lim / sqrtf(l2);
+          s1 *= scl;
+          s2 *= scl;
+        }
+        const float d1 = s1 - app[i][1], d2 = s2 - app[i][2];
+        app[i][1] = s1;
+        app[i][2] = s2;
+        dv.y -= d1 * inv_m;
+        dv.x += d2 * inv_m;
+        const float q1 = d1 * inv_i, q2 = d2 * inv_i;
+        dw.x += r[i].z * q1;
+        dw.y += r[i].z * q2;
+        dw.z -= r[i].x * q1 + r[i].y * q2;
+        const float e1 = d1 * den[i][1], e2 = d2 * den[i][2];
+        resid = fmaxf(resid, fmaxf(e1 * e1, e2 * e2));
+      }
+    }
+    if (resid <= PH_RESID) break;
+  }
+  VelPair o;
+  o.v = v + dv;
+  o.w = w + dw;
+  return o;
+}
+
+// general contact set of the cube (walls, ceiling, more than the plane manifold), out of line
+__device__ __noinline__ VelPair solve_contacts_cube_call(const Contact* c, int nc, float restitution, f3 v, f3 w) {
+  solve_contacts<SHAPE_CUBE>(c, nc, restitution, v, w);
+  VelPair o;
+  o.v = v;
+  o.w = w;
+  return o;
 }
 
 // ---------------------------------------------------------------- sphere: single-contact fast path
@@ -550,7 +648,6 @@ __device__ __noinline__ void sphere_solve_generic(const f3* n, const float* dist
 // Contacts that do need the iterative solver (10-15 % of the two-contact substeps of a filter run, and every
 // corner): out of line, so that the registers of the hot loop are sized by the free-flight / single-contact path.
 // Everything travels by value: taking the address of the caller's Body would pin it to local memory.
-struct VelPair { f3 v, w; };
 __device__ __noinline__ VelPair sphere_solve_iter(float ceil_half, float restitution, f3 x, f3 v, f3 w) {
   ScenePar sp;
   sp.ceil_half = ceil_half;
@@ -584,10 +681,13 @@ __device__ __forceinline__ void integrate_q(Body& s) {
   const float dt = PH_DT;
   float ang = sqrtf(dot3(s.w, s.w));
   if (ang * dt > PH_ANG_THRESH) ang = 0.5f * 1.57079632679489661923f / dt;
-  f3 ax;
-  if (ang < 0.001f) ax = s.w * (0.5f * dt - (dt * dt * dt) * 0.020833333333f * ang * ang);
-  else ax = s.w * (sinf(0.5f * ang * dt) / ang);
-  float cw = cosf(ang * dt * 0.5f);
+  // half angle hh <= pi/8 after the clamp: sin(hh)/ang = (dt/2) sinc(hh) and cos(hh) as even polynomials in hh
+  // (truncation < 1e-11, i.e. below float rounding; Bullet's own small-angle branch is the first two terms), which
+  // is branch free and keeps libm's range-reduction slow paths out of the kernels' instruction footprint
+  const float hh = 0.5f * ang * dt, h2 = hh * hh;
+  const float sinc = 1.0f + h2 * (-1.0f / 6.0f + h2 * (1.0f / 120.0f + h2 * (-1.0f / 5040.0f + h2 * (1.0f / 362880.0f))));
+  const float cw = 1.0f + h2 * (-0.5f + h2 * (1.0f / 24.0f + h2 * (-1.0f / 720.0f + h2 * (1.0f / 40320.0f))));
+  const f3 ax = s.w * (0.5f * dt * sinc);
   f4 q = s.q, r;
   r.x = cw * q.x + ax.x * q.w + ax.y * q.z - ax.z * q.y;
   r.y = cw * q.y - ax.x * q.z + ax.y * q.w + ax.z * q.x;
@@ -617,8 +717,14 @@ __device__ __forceinline__ void substep(const ScenePar& sp, float restitution, B
     int nc = 0;
     if (!clear) nc = collide_cube(sp, s, pm, c);
     else pm.n = 0;
+    const int npl = pm.n;  // the plane-manifold points come first in c[]
     apply_forces(s);
-    if (nc > 0) solve_contacts<SHAPE>(c, nc, restitution, s.v, s.w);
+    if (nc > 0) {
+      const VelPair r = (nc == npl) ? solve_plane_contacts(c, nc, restitution, s.v, s.w)
+                                    : solve_contacts_cube_call(c, nc, restitution, s.v, s.w);
+      s.v = r.v;
+      s.w = r.w;
+    }
   }
   s.x = s.x + s.v * dt;
   if (TRACK_Q || SHAPE == SHAPE_CUBE) integrate_q(s);

@@ -419,9 +419,11 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
 struct ChainOut {
   double qs;
   f3 x, v, w;
+  f4 q;
 };
-__device__ __noinline__ ChainOut resimulate_sphere_call(float ceil_half, f3 x0, f3 v0, int S, float e,
-                                                        const float* __restrict__ xt, int64_t n, int64_t i, int steps) {
+template <int SHAPE>
+__device__ __noinline__ ChainOut resimulate_call(float ceil_half, f3 x0, f3 v0, int S, float e,
+                                                 const float* __restrict__ xt, int64_t n, int64_t i, int steps) {
   ScenePar sp;
   sp.ceil_half = ceil_half;
   TrialPar tp;
@@ -429,11 +431,14 @@ __device__ __noinline__ ChainOut resimulate_sphere_call(float ceil_half, f3 x0, 
   tp.v0[0] = v0.x; tp.v0[1] = v0.y; tp.v0[2] = v0.z;
   Body s;
   ChainOut o;
-  o.qs = resimulate<SHAPE_SPHERE, false, false>(sp, tp, S, e, xt, n, i, steps, s, nullptr);
-  o.x = s.x; o.v = s.v; o.w = s.w;
+  o.qs = resimulate<SHAPE, SHAPE == SHAPE_CUBE, false>(sp, tp, S, e, xt, n, i, steps, s, nullptr);
+  o.x = s.x; o.v = s.v; o.w = s.w; o.q = s.q;
   return o;
 }
 
+#ifndef RJ_MINB_CUBE
+#define RJ_MINB_CUBE 4  // cube: 16 warps at 128 registers
+#endif
 #ifndef RJ_BLOCK
 #define RJ_BLOCK 128
 #endif
@@ -450,7 +455,7 @@ __device__ __noinline__ ChainOut resimulate_sphere_call(float ceil_half, f3 x0, 
 // independent (no shared memory, no barriers): contact response that needs no iteration is in line, the rest is
 // an out-of-line call (physics.cuh).  A sphere's orientation is not integrated here: it never feeds back.
 template <int SHAPE>
-__global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : 1)
+__global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : RJ_MINB_CUBE)
     k_rejuvenate(Bufs B, const Ctl* ctl, TrialPar tp, ScenePar sp, int64_t n, int64_t goff, u64 seed, int t, int S,
                  int R, double prop_sigma, u64* accept_out) {
   const int cur = ctl->cur ^ ctl->resampled;
@@ -468,16 +473,11 @@ __global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : 1)
       const double fwd = truncnorm_logpdf(e_new, e_old, prop_sigma, 0.0, 1.0);
       const double bwd = truncnorm_logpdf(e_old, e_new, prop_sigma, 0.0, 1.0);
       const double log_u = log(u01(r[1]));
+      const ChainOut o = resimulate_call<SHAPE>(sp.ceil_half, mk3(tp.x0[0], tp.x0[1], tp.x0[2]),
+                                                mk3(tp.v0[0], tp.v0[1], tp.v0[2]), S, (float)e_new, xt_cur, n, i, t + 1);
+      const double q_new = o.qs;
       Body s;
-      double q_new;
-      if (SHAPE == SHAPE_SPHERE) {
-        const ChainOut o = resimulate_sphere_call(sp.ceil_half, mk3(tp.x0[0], tp.x0[1], tp.x0[2]),
-                                                  mk3(tp.v0[0], tp.v0[1], tp.v0[2]), S, (float)e_new, xt_cur, n, i, t + 1);
-        q_new = o.qs;
-        s.x = o.x; s.v = o.v; s.w = o.w;
-      } else {
-        q_new = resimulate<SHAPE, true, false>(sp, tp, S, (float)e_new, xt_cur, n, i, t + 1, s, nullptr);
-      }
+      s.x = o.x; s.v = o.v; s.w = o.w; s.q = o.q;
       const double alpha = -(q_new - q_old) * inv2s2 - fwd + bwd;
       if (log_u < alpha) {
         // accepted: the simulator state goes out right away, so nothing but (e, q) stays live across the moves

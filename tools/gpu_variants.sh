@@ -6,7 +6,7 @@ timeout 300 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu_$R.log 2
 for so in smc_physics_b200/libsmcphys.so smc_physics_b200/libsmcphys_v*.so; do
   [ -f "$so" ] || continue
   echo "== $so"
-  SMCPHYS_SO=$PWD/$so timeout 150 python bench.py --steps 1 --warmup 3 --no-cpu-baseline 2>&1 | python -c "
+  SMCPHYS_SO=$PWD/$so timeout 150 python bench.py --steps 1 --warmup 3 --no-cpu-baseline ${BENCH_ARGS:-} 2>&1 | python -c "
 import sys, json
 for l in sys.stdin:
     if l.startswith('{'):
