@@ -316,8 +316,69 @@ def run_inference(fname, args, output_path, w1=None, w2=None):
     return results
 
 
-def main(args=None, fnames=None):
-    """main.jl:18-85 on one process: list + sort the trials, build the output directory, run every trial."""
+def run_inference_batch(fnames, args, output_path, max_concurrent=None, memory_budget=96e9):
+    """Many trials at once on one GPU - the stand-in for the reference's `pmap` over 15 worker processes
+    (main.jl:7,54) and BASELINE.json's "all trials concurrent" configuration.  Every trial gets its own filter
+    handle, and a handle owns its own CUDA stream; `run_smc` only enqueues work (the resampling decision is taken
+    on the device), so enqueueing all trials of a wave before reading any result lets their kernels overlap and
+    fill the GPU even when one trial's particles do not.  Waves are sized by device memory.  Outputs are identical
+    to calling run_inference on each trial in turn (same seeds, same files); per-step particle dumps
+    (save_particles) need a host round trip per step and fall back to the sequential path."""
+    if args.algorithm != "SMC":
+        raise NotImplementedError("algorithm=%r: only the SMC path is on the B200 hot path" % args.algorithm)
+    if args.save_particles:
+        return [run_inference(f, args, output_path) for f in fnames]
+    bullet = "Bullet" in args.expt_id
+    trials = []
+    for f in fnames:
+        if bullet:
+            sim = CudaSim(step_dur=1 / 60, device=args.device)
+            path = os.path.join(DATA_ROOT, "Data/BulletStimulus/New/", args.expt_id.split("_")[1], f)
+        else:
+            sim = CudaSim(step_dur=1 / 30, device=args.device)
+            path = os.path.join(DATA_ROOT, "Data/RealFlowData/", args.expt_id, f)
+        init_position, _, init_velocity, obs, t_s = read_obs_file(path, "Bullet" if bullet else "RealFlow", args.algorithm)
+        init_target_state(sim, args.target_id, init_position, init_velocity)
+        trials.append((path, sim, init_position, init_velocity, obs, t_s))
+    per_trial = lambda T: args.num_particles * (24.0 * max(T, 1) + 260.0)   # two history buffers + state, bytes
+    result_dir = os.path.join(output_path, "inferences/")
+    os.makedirs(os.path.join(output_path, "intermediate/"), exist_ok=True)
+    os.makedirs(result_dir, exist_ok=True)
+    results, i = [], 0
+    while i < len(trials):
+        wave, used = [], 0.0
+        while i < len(trials) and (not wave or (used + per_trial(trials[i][5]) <= memory_budget and
+                                               (max_concurrent is None or len(wave) < max_concurrent))):
+            used += per_trial(trials[i][5])
+            wave.append(trials[i])
+            i += 1
+        pfs = []
+        for path, sim, ip, iv, obs, t_s in wave:       # enqueue everything ...
+            pf = api.ParticleFilter(num_particles=args.num_particles, shape=sim.shape, substeps=sim.substeps,
+                                    max_timesteps=max(t_s, 1), rejuvenation_moves=args.rejuvenation_moves,
+                                    observation_noise=Args().observation_noise, transition_noise=Args().transition_noise,
+                                    ceiling_half=sim.ceiling_half, device=sim.device, seed=args.seed)
+            pf.set_trial(np.asarray(ip, float), np.asarray(iv, float), np.asarray(obs, float).reshape(-1, 3)[:t_s])
+            pf.run_smc(args.rejuvenation_moves, want_stats=False)
+            pfs.append(pf)
+        for (path, sim, ip, iv, obs, t_s), pf in zip(wave, pfs):   # ... then collect
+            out = pf.get_particles(want_traj=True, steps=t_s)
+            res = Particles(out["e"], out["score"], out["traj"], out["log_w"], pf)
+            tokens = os.path.basename(path).split("_")
+            write_to_csv(res, os.path.join(result_dir, "%s_%s" % (tokens[1], tokens[2])))
+            if args.predict:
+                ppd = predict(res, args.prediction_timesteps)
+                os.makedirs(os.path.join(output_path, "Predictions/"), exist_ok=True)
+                write_to_csv(ppd, os.path.join(output_path, "Predictions/", "predictions_%s_%s" % (tokens[1], tokens[2])))
+            pf.close()
+            res.pf = None
+            results.append(res)
+    return results
+
+
+def main(args=None, fnames=None, concurrent=False):
+    """main.jl:18-85 on one process: list + sort the trials, build the output directory, run every trial
+    (concurrent=True: all trials of a wave in flight at once, run_inference_batch)."""
     args = args or Args()
     if "Bullet" in args.expt_id:
         d = os.path.join(DATA_ROOT, "Data/BulletStimulus/New/", args.expt_id.split("_")[1])
@@ -329,4 +390,6 @@ def main(args=None, fnames=None):
     out = make_directories("/".join([args.expt_id, args.model_id, args.target_id, generate_noise_id(args),
                                      args.algorithm, generate_inference_param_id(args), "Data"]))
     print("Output Filepath... ", out)
+    if concurrent:
+        return run_inference_batch(names, args, out)
     return [run_inference(f, args, out) for f in names]
