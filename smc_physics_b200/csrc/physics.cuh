@@ -157,8 +157,18 @@ __device__ __forceinline__ int collide_cube(const ScenePar& sp, const Body& s, M
     }
     for (int i = 0; i < pm.n; i++) { out[nc].r = wa[i] - s.x; out[nc].n = mk3(0.f, 0.f, 1.f); out[nc].dist = dist[i]; nc++; }
   }
+  // only a box whose inner face is within the bounding radius of the centre can overlap the cube (the exact
+  // overlap test below would reject the others anyway): usually none when the cube is on the floor
+  const float rad = 1.7320508075688772f * h + 1e-6f;
+  unsigned int near = 0;
+  if (s.x.x < -0.5f + rad) near |= 1u;
+  if (s.x.y > 0.5f - rad) near |= 2u;
+  if (s.x.x > 0.5f - rad) near |= 4u;
+  if (s.x.y < -0.5f + rad) near |= 8u;
+  if (s.x.z > 1.01f - sp.ceil_half - rad) near |= 16u;
 #pragma unroll 1
   for (int b = 0; b < 5; b++) {
+    if (!((near >> b) & 1u)) continue;
     f3 c, bh;
     static_box(b, sp.ceil_half, c, bh);
     f3 d = s.x - c;
