@@ -308,10 +308,14 @@ struct VelPair { f3 v, w; };
 __device__ __noinline__ VelPair solve_plane_contacts(const Contact* c, int nc, float restitution, f3 v, f3 w) {
   const float inv_m = PH_INV_M, inv_i = PH_INV_I_CUBE;
   const float crest = restitution * PH_STATIC_REST;
+  // slots beyond the largest contact count in the warp are skipped by a uniform branch: nine tenths of the plane
+  // contact sets are a single point (the manifold starts cold at every macro step and gains one point per substep)
+  const int ncw = __reduce_max_sync(__activemask(), nc);
   f3 r[4];
   float den[4][3], dinv[4][3], rhs[4][3], app[4][3];
 #pragma unroll
   for (int i = 0; i < 4; i++) {
+    if (i >= ncw) break;
     if (i < nc) {
       r[i] = c[i].r;
       const float rx2 = r[i].x * r[i].x, ry2 = r[i].y * r[i].y, rz2 = r[i].z * r[i].z;
@@ -339,6 +343,7 @@ __device__ __noinline__ VelPair solve_plane_contacts(const Contact* c, int nc, f
     float resid = 0.f;
 #pragma unroll
     for (int i = 0; i < 4; i++) {
+      if (i >= ncw) break;
       if (i < nc) {
         float dimp = rhs[i][0] - (dv.z + (r[i].y * dw.x - r[i].x * dw.y)) * dinv[i][0];
         const float sum = app[i][0] + dimp;
@@ -354,6 +359,7 @@ __device__ __noinline__ VelPair solve_plane_contacts(const Contact* c, int nc, f
     }
 #pragma unroll
     for (int i = 0; i < 4; i++) {
+      if (i >= ncw) break;
       if (i < nc) {
         const float lim = PH_FRICTION * app[i][0];
         float s1 = app[i][1] + (rhs[i][1] - (-dv.y + (r[i].z * dw.x - r[i].x * dw.z)) * dinv[i][1]);
@@ -377,64 +383,6 @@ __device__ __noinline__ VelPair solve_plane_contacts(const Contact* c, int nc, f
         resid = fmaxf(resid, fmaxf(e1 * e1, e2 * e2));
       }
     }
-    if (resid <= PH_RESID) break;
-  }
-  VelPair o;
-  o.v = v + dv;
-  o.w = w + dw;
-  return o;
-}
-
-// One plane-manifold point: nine tenths of the cube's plane contact sets (the manifold starts cold at every macro
-// step and gains at most one point per substep), 2.3 sweeps on average.  Same rows as above for i = 0, scalar state.
-__device__ __noinline__ VelPair solve_plane_one(f3 r, float dist, float restitution, f3 v, f3 w) {
-  const float inv_m = PH_INV_M, inv_i = PH_INV_I_CUBE;
-  const float rx2 = r.x * r.x, ry2 = r.y * r.y, rz2 = r.z * r.z;
-  const float den0 = inv_m + (ry2 + rx2) * inv_i, den1 = inv_m + (rz2 + rx2) * inv_i, den2 = inv_m + (rz2 + ry2) * inv_i;
-  const float dinv0 = 1.0f / den0, dinv1 = 1.0f / den1, dinv2 = 1.0f / den2;
-  const float relv0 = v.z + (r.y * w.x - r.x * w.y);
-  const float relv1 = -v.y + (r.z * w.x - r.x * w.z);
-  const float relv2 = v.x + (r.z * w.y - r.y * w.z);
-  float rest = 0.f;
-  if (fabsf(relv0) >= PH_REST_THRESH) rest = fmaxf(0.f, -(restitution * PH_STATIC_REST) * relv0);
-  const float distance = dist + PH_SLOP;
-  float verr = rest - relv0, perr = 0.f;
-  if (distance > 0.f) verr -= distance / PH_DT;
-  else perr = -distance * PH_ERP / PH_DT;
-  const float rhs0 = (perr + verr) * dinv0, rhs1 = -relv1 * dinv1, rhs2 = -relv2 * dinv2;
-  float app0 = 0.f, app1 = 0.f, app2 = 0.f;
-  f3 dv = mk3(0.f, 0.f, 0.f), dw = mk3(0.f, 0.f, 0.f);
-  for (int it = 0; it < PH_ITERS; it++) {
-    float dimp = rhs0 - (dv.z + (r.y * dw.x - r.x * dw.y)) * dinv0;
-    const float sum = app0 + dimp;
-    if (sum < 0.f) { dimp = -app0; app0 = 0.f; }
-    else app0 = sum;
-    dv.z += dimp * inv_m;
-    const float q = dimp * inv_i;
-    dw.x += r.y * q;
-    dw.y -= r.x * q;
-    const float dvel = dimp * den0;
-    float resid = dvel * dvel;
-    const float lim = PH_FRICTION * app0;
-    float s1 = app1 + (rhs1 - (-dv.y + (r.z * dw.x - r.x * dw.z)) * dinv1);
-    float s2 = app2 + (rhs2 - (dv.x + (r.z * dw.y - r.y * dw.z)) * dinv2);
-    const float l2 = s1 * s1 + s2 * s2;
-    if (l2 > lim * lim) {
-      const float scl = lim / sqrtf(l2);
-      s1 *= scl;
-      s2 *= scl;
-    }
-    const float d1 = s1 - app1, d2 = s2 - app2;
-    app1 = s1;
-    app2 = s2;
-    dv.y -= d1 * inv_m;
-    dv.x += d2 * inv_m;
-    const float q1 = d1 * inv_i, q2 = d2 * inv_i;
-    dw.x += r.z * q1;
-    dw.y += r.z * q2;
-    dw.z -= r.x * q1 + r.y * q2;
-    const float e1 = d1 * den1, e2 = d2 * den2;
-    resid = fmaxf(resid, fmaxf(e1 * e1, e2 * e2));
     if (resid <= PH_RESID) break;
   }
   VelPair o;
@@ -788,10 +736,8 @@ __device__ __forceinline__ void substep(const ScenePar& sp, float restitution, B
     const int npl = pm.n;  // the plane-manifold points come first in c[]
     apply_forces(s);
     if (nc > 0) {
-      VelPair r;
-      if (nc == 1 && npl == 1) r = solve_plane_one(c[0].r, c[0].dist, restitution, s.v, s.w);
-      else if (nc == npl) r = solve_plane_contacts(c, nc, restitution, s.v, s.w);
-      else r = solve_contacts_cube_call(c, nc, restitution, s.v, s.w);
+      const VelPair r = (nc == npl) ? solve_plane_contacts(c, nc, restitution, s.v, s.w)
+                                    : solve_contacts_cube_call(c, nc, restitution, s.v, s.w);
       s.v = r.v;
       s.w = r.w;
     }
