@@ -72,6 +72,38 @@ def test_contact_macro_step_vs_f32_oracle(sp, shape, tol):
         assert np.median(err) < 1e-6
 
 
+def test_sphere_two_contact_screening_vs_iterative_oracle(sp):
+    """The in-line screening of two-contact substeps (physics.cuh sphere_contacts_inline: neither contact pushes /
+    exactly one pushes and the other stays idle -> closed form) against the oracle, which always iterates.
+    Balls placed in the floor / wall corner band - resting, separating, approaching, penetrating, also under the
+    wall - one 1/240 s substep, velocities compared.  The bar: what DESIGN.md claims for the screening (rounding
+    level, < 1e-5 m/s incl. float32 noise of the general path) on >= 99 % of the bodies, the rest being the
+    early-exit cases of the iterative path (steady-state exit) at < 1e-3 m/s."""
+    rng = np.random.default_rng(21)
+    n = 6000
+    st = np.zeros((n, 13), np.float32)
+    side = rng.integers(0, 4, n)
+    a = rng.uniform(0.43, 0.53, n)                      # distance of the centre from the arena centre, across a wall
+    b = rng.uniform(-0.4, 0.4, n)
+    st[:, 0] = np.where(side == 0, a, np.where(side == 1, -a, b))
+    st[:, 1] = np.where(side == 2, a, np.where(side == 3, -a, b))
+    st[:, 2] = rng.uniform(-0.02, 0.056, n)              # floor band: penetrating ... just inside the breaking threshold
+    st[:, 6] = 1.0
+    st[:, 7:10] = rng.uniform(-1.5, 1.5, (n, 3)) * rng.choice([0.0, 0.05, 1.0], (n, 1))   # resting, creeping, moving
+    st[:, 10:13] = rng.uniform(-8, 8, (n, 3)) * rng.choice([0.0, 1.0], (n, 1))
+    e = rng.uniform(0, 1, n).astype(np.float32)
+    out = sp.sim_step(0, st, e, S=1)
+    ref = np.stack([orc.sim_raw(0, float(e[i]), st[i].astype(np.float64), 1, f32=True)[0] for i in range(n)])
+    dv = np.abs(out[:, 7:10] - ref[:, 7:10]).max(axis=1)
+    dw = np.abs(out[:, 10:13] - ref[:, 10:13]).max(axis=1) * 0.05
+    err = np.maximum(dv, dw)
+    assert np.isfinite(out).all()
+    moved = np.abs(ref[:, 7:13] - st[:, 7:13].astype(np.float64)).max(axis=1) > 0.05
+    assert moved.mean() > 0.3, "the poses must actually produce contact impulses"
+    assert (err < 1e-5).mean() > 0.99, ((err < 1e-5).mean(), np.sort(err)[-8:])
+    assert err.max() < 1e-3, np.sort(err)[-8:]
+
+
 @pytest.mark.parametrize("shape,S,tol", [(0, 5, 1e-4), (0, 9, 1e-4), (1, 5, 1e-3)])
 def test_T1_trajectories_identical_noise(sp, shape, S, tol):
     rng = np.random.default_rng(10 + shape + S)
