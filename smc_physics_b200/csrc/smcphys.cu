@@ -437,7 +437,7 @@ __device__ __noinline__ ChainOut resimulate_call(float ceil_half, f3 x0, f3 v0, 
 }
 
 #ifndef RJ_MINB_CUBE
-#define RJ_MINB_CUBE 4  // cube: 16 warps at 128 registers
+#define RJ_MINB_CUBE 5  // cube: 20 warps at 96 registers (4..7 measured within 5 %)
 #endif
 #ifndef RJ_BLOCK
 #define RJ_BLOCK 128
