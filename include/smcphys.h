@@ -125,6 +125,10 @@ int smcphys_pf_unpack(smcphys_handle* h, int32_t t, const float* d_recv, int32_t
 /* single-shard resampling step with the decision taken on the device (no host synchronisation) */
 int smcphys_pf_resample_local(smcphys_handle* h, int32_t t);
 int smcphys_pf_rejuvenate(smcphys_handle* h, int32_t t, int32_t R, uint64_t* d_accept_count /* may be NULL */);
+/* The same with the moves numbered move0 .. move0+R-1 in the Philox counter, so that a long chain of MH moves at a
+ * fixed step can be issued in pieces with results read in between: gaussian_drift_mcmc (Inference/mcmc.jl:53-93,
+ * 1000 moves at t = T, the last 100 recorded). */
+int smcphys_pf_rejuvenate_from(smcphys_handle* h, int32_t t, int32_t R, int32_t move0, uint64_t* d_accept_count);
 int smcphys_synchronize(smcphys_handle* h);
 
 /* ---- stateless entries (host pointers), used for parity checks and the PhySMC simulator interface */

@@ -65,6 +65,7 @@ SIGNATURES = {
     "smcphys_pf_unpack": (C.c_int, [_H, C.c_int32, C.c_void_p, C.c_int32, _ip, _ip, _ip]),
     "smcphys_pf_resample_local": (C.c_int, [_H, C.c_int32]),
     "smcphys_pf_rejuvenate": (C.c_int, [_H, C.c_int32, C.c_int32, C.c_void_p]),
+    "smcphys_pf_rejuvenate_from": (C.c_int, [_H, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]),
     "smcphys_synchronize": (C.c_int, [_H]),
     "smcphys_sim_step": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_int64, _fp, _fp]),
     "smcphys_simulate": (C.c_int, [C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double, _dp, _dp, _fp, _fp,

@@ -197,8 +197,8 @@ class ParticleFilter:
     def pf_resample_local(self, t):
         check(lib().smcphys_pf_resample_local(self._h, t))
 
-    def pf_rejuvenate(self, t, R, d_accept=None):
-        check(lib().smcphys_pf_rejuvenate(self._h, t, R, C.c_void_p(d_accept)))
+    def pf_rejuvenate(self, t, R, d_accept=None, move0=0):
+        check(lib().smcphys_pf_rejuvenate_from(self._h, t, R, move0, C.c_void_p(d_accept)))
 
 
 K_EXTEND, K_WEIGHTS, K_GATHER, K_REJUVENATE = 0, 1, 2, 3

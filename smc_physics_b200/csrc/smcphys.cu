@@ -457,7 +457,7 @@ __device__ __noinline__ ChainOut resimulate_call(float ceil_half, f3 x0, f3 v0, 
 template <int SHAPE>
 __global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : RJ_MINB_CUBE)
     k_rejuvenate(Bufs B, const Ctl* ctl, TrialPar tp, ScenePar sp, int64_t n, int64_t goff, u64 seed, int t, int S,
-                 int R, double prop_sigma, u64* accept_out) {
+                 int R, int move0, double prop_sigma, u64* accept_out) {
   const int cur = ctl->cur ^ ctl->resampled;
   const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   unsigned int acc = 0;
@@ -468,7 +468,7 @@ __global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : RJ
     const float* xt_cur = B.xt[cur];
     for (int j = 0; j < R; j++) {
       uint32_t r[4];
-      philox4x32_10(seed, (uint32_t)(goff + i), (uint32_t)t, (uint32_t)j, (uint32_t)ST_PROPOSAL, r);
+      philox4x32_10(seed, (uint32_t)(goff + i), (uint32_t)t, (uint32_t)(move0 + j), (uint32_t)ST_PROPOSAL, r);
       const double e_new = truncnorm_sample(u01(r[0]), e_old, prop_sigma, 0.0, 1.0);
       const double fwd = truncnorm_logpdf(e_new, e_old, prop_sigma, 0.0, 1.0);
       const double bwd = truncnorm_logpdf(e_old, e_new, prop_sigma, 0.0, 1.0);
@@ -975,19 +975,22 @@ int smcphys_pf_resample_local(smcphys_handle* h, int32_t t) {
 }
 
 int smcphys_pf_rejuvenate(smcphys_handle* h, int32_t t, int32_t R, uint64_t* d_accept_count) {
+  return smcphys_pf_rejuvenate_from(h, t, R, 0, d_accept_count);
+}
+int smcphys_pf_rejuvenate_from(smcphys_handle* h, int32_t t, int32_t R, int32_t move0, uint64_t* d_accept_count) {
   NEED_TRIAL(h);
   if (t != h->steps_done - 1) return fail(SMCPHYS_ESTATE, "pf_rejuvenate: t is not the current step");
-  if (R < 0) return fail(SMCPHYS_EINVAL, "R < 0");
+  if (R < 0 || move0 < 0) return fail(SMCPHYS_EINVAL, "R < 0 or move0 < 0");
   if (R == 0) return 0;
   const int64_t n = h->cfg.num_particles;
   u64* acc = d_accept_count ? (u64*)d_accept_count : h->d_acc + t;
   ProfScope ps(h, SMCPHYS_K_REJUVENATE);
   if (h->cfg.shape == SMCPHYS_SPHERE)
     LAUNCH(k_rejuvenate<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B, h->ctl, h->tp, h->sp, n,
-           h->cfg.particle_offset, h->cfg.seed, t, h->cfg.substeps, R, h->cfg.proposal_sigma, acc);
+           h->cfg.particle_offset, h->cfg.seed, t, h->cfg.substeps, R, move0, h->cfg.proposal_sigma, acc);
   else
     LAUNCH(k_rejuvenate<SHAPE_CUBE>, nblk(n, RJ_BLOCK), RJ_BLOCK, h->stream, h->B, h->ctl, h->tp, h->sp, n,
-           h->cfg.particle_offset, h->cfg.seed, t, h->cfg.substeps, R, h->cfg.proposal_sigma, acc);
+           h->cfg.particle_offset, h->cfg.seed, t, h->cfg.substeps, R, move0, h->cfg.proposal_sigma, acc);
   return 0;
 }
 

@@ -279,6 +279,42 @@ def predict(particles, T):
                      particles.pf)
 
 
+# ------------------------------------------------------------------ Inference/mcmc.jl
+def gaussian_drift_mcmc(model, gm_args, obs, runs=1000, keep=100, chains=1, args=None):
+    """mcmc.jl:53-93: one trace generated from the prior and conditioned on the observations (`generate`, :56), then
+    `runs` Metropolis-Hastings moves on the elasticity with the particle filter's Gaussian-drift proposal
+    (`mh(trace, proposal, ())`, :68), each a full re-simulation of the T steps; returns (mean elasticity of the last
+    `keep` moves, the last `keep` states as Particles: one row per recorded move).  `chains` > 1 runs that many
+    independent chains side by side (the GPU's way of using the hardware; the reference runs one) and averages them.
+    On the device this is the rejuvenation kernel at the fixed step T: the first runs - keep moves in one launch, then
+    one launch per recorded move (smcphys_pf_rejuvenate_from keeps the Philox move numbering)."""
+    sim, init_state, T = gm_args
+    args = args or Args()
+    obs = np.asarray(obs, dtype=np.float64).reshape(-1, 3)[:T]
+    pf = api.ParticleFilter(num_particles=chains, shape=sim.shape, substeps=sim.substeps, max_timesteps=max(T, 1),
+                            rejuvenation_moves=1, observation_noise=Args().observation_noise,
+                            transition_noise=Args().transition_noise, ceiling_half=sim.ceiling_half, device=sim.device,
+                            seed=args.seed)
+    k = init_state.kinematics
+    pf.set_trial(np.asarray(k.position, float).reshape(3), np.asarray(k.linear_vel, float).reshape(3), obs)
+    pf.pf_init()
+    for t in range(T):                      # generate(): every step extended from the prior, no resampling
+        pf.pf_extend(t)
+    burn = max(runs - keep, 0)
+    if burn:
+        pf.pf_rejuvenate(T - 1, burn, move0=0)
+    es, scores, trajs = [], [], []
+    for i in range(runs - burn):
+        pf.pf_rejuvenate(T - 1, 1, move0=burn + i)
+        out = pf.get_particles(want_traj=True, steps=T)
+        es.append(out["e"].copy()); scores.append(out["score"].copy()); trajs.append(out["traj"].copy())
+    pf.close()
+    e = np.stack(es)                        # [keep, chains]
+    avg_last = float(e.mean())
+    results = Particles(e.reshape(-1), np.stack(scores).reshape(-1), np.concatenate(trajs, axis=2))
+    return avg_last, results
+
+
 # ------------------------------------------------------------------ Inference/run_inference.jl
 def run_inference(fname, args, output_path, w1=None, w2=None):
     """run_inference.jl:19-124: one trial -> <output_path>inferences/<Ela>_<Var>.csv (+ intermediate/ dumps)."""
@@ -292,8 +328,15 @@ def run_inference(fname, args, output_path, w1=None, w2=None):
     init_position, _, init_velocity, obs, t_s = read_obs_file(fname, source, args.algorithm)
     init_state = init_target_state(sim, args.target_id, init_position, init_velocity)
     sim_args = (sim, init_state, t_s)
+    if args.algorithm == "MCMC":            # run_inference.jl:56-68
+        print("Initializing MCMC")
+        avg_last_hundred, results = gaussian_drift_mcmc(generate_trajectory, sim_args, obs, args=args)
+        print("Elasticity estimate: ", avg_last_hundred)
+        tokens = os.path.basename(fname).split("_")
+        write_to_csv(results, os.path.join(output_path, "%s_%s" % (tokens[1], tokens[2])))
+        return results
     if args.algorithm != "SMC":
-        raise NotImplementedError("algorithm=%r: only the SMC path is on the B200 hot path (SURVEY.md section 8)"
+        raise NotImplementedError("algorithm=%r: the DEBUG mode opens PyBullet's GUI (unavailable on this box)"
                                   % args.algorithm)
     print("Initializing Particle Filter")
     particle_dir = os.path.join(output_path, "intermediate/")
