@@ -279,6 +279,68 @@ def predict(particles, T):
                      particles.pf)
 
 
+# ------------------------------------------------------------------ Tests/generate_trajectories.jl
+def _quat_from_euler(roll, pitch, yaw):
+    """PyBullet getQuaternionFromEuler (xyzw; rotation = Rz(yaw) Ry(pitch) Rx(roll))."""
+    cr, sr, cp, sp_, cy, sy = (math.cos(roll / 2), math.sin(roll / 2), math.cos(pitch / 2), math.sin(pitch / 2),
+                               math.cos(yaw / 2), math.sin(yaw / 2))
+    return [sr * cp * cy - cr * sp_ * sy, cr * sp_ * cy + sr * cp * sy, cr * cp * sy - sr * sp_ * cy,
+            cr * cp * cy + sr * sp_ * sy]
+
+
+def generate_trajectories(obj_type="Sphere", seed=20240830, device=0):
+    """Tests/generate_trajectories.jl:107-212 on the CUDA simulator: the 27 stimuli (elasticity 0.1 ... 0.9, three
+    variations each) of the BulletTest_<obj_type> experiments that main.jl:26 expects under
+    Data/BulletStimulus/New/<obj_type>/ and the reference repository does not ship.  Initial position U[-0.4,0.4]^2 x
+    [0.1,0.9], Euler orientation U[0,2pi]^3, velocity U[-5,5]^3 (:73-89); one PhySMC.step (1/60 s) per frame until
+    120 frames or every velocity component is within 0.1 (:184); positions truncated to 5 digits (:175,:208); the
+    ceiling slab is 0.02 thick here (:52).  The reference draws from an unseeded RNG; `seed` makes the set
+    reproducible.  Writes <obj>_Ela<e>_Var<v>.csv (initial state, the column layout read_obs_file expects) next to
+    <obj>_Ela<e>_Var<v>_observed.csv, and the initial-state file also where the reference puts it (one level up)."""
+    rng = np.random.default_rng(seed)
+    sim = CudaSim(step_dur=1 / 60, device=device, ceiling_half=0.02)
+    sim.shape = api.SPHERE if obj_type.lower().startswith("sphere") else api.CUBE
+    d_init = os.path.join(DATA_ROOT, "Data/BulletStimulus", obj_type)
+    d_new = os.path.join(DATA_ROOT, "Data/BulletStimulus/New", obj_type)
+    os.makedirs(d_init, exist_ok=True)
+    os.makedirs(d_new, exist_ok=True)
+    names, pos, quat, vel, ela = [], [], [], [], []
+    for i in range(3, 30):
+        e_idx, var = i // 3, i % 3 + 1
+        p = [rng.uniform(-0.4, 0.4), rng.uniform(-0.4, 0.4), rng.uniform(0.1, 0.9)]
+        eul = [rng.uniform(0, 2 * math.pi) for _ in range(3)]
+        v = [rng.uniform(-5, 5) for _ in range(3)]
+        name = "%s_Ela%d_Var%d" % (obj_type, e_idx, var)
+        header = "Date,SceneID,Elasticity,Variation,PositionX,PositionY,PositionZ,RotationX,RotationY,RotationZ," \
+                 "VelocityX,VelocityY,VelocityZ\n"
+        row = "2024-08-30,Cube_Ela%dVar_%d,%s,%d,%s\n" % (e_idx, var, _jl_float(0.1 * e_idx), var,
+                                                         ",".join(_jl_float(x) for x in p + eul + v))
+        for d in (d_init, d_new):
+            with open(os.path.join(d, name + ".csv"), "w") as f:
+                f.write(header + row)
+        names.append(name); pos.append(p); quat.append(_quat_from_euler(*eul)); vel.append(v); ela.append(0.1 * e_idx)
+    n = len(names)
+    kin = RigidBodyState(np.array(pos), np.array(quat), np.array(vel), np.zeros((n, 3)))
+    st = CudaState(kinematics=kin, latents={"restitution": np.array(ela, F32), "mass": 1.0, "lateralFriction": 0.5})
+    alive = np.ones(n, bool)
+    traj = [[] for _ in range(n)]
+    v_now = np.array(vel)
+    for t in range(120):
+        alive &= (np.abs(v_now) > 0.1).any(axis=1)
+        if not alive.any():
+            break
+        st = step(sim, st)                  # all 27 bodies in one batch; a stopped body's further steps are ignored
+        v_now = st.kinematics.linear_vel
+        for b in np.where(alive)[0]:
+            traj[b].append(st.kinematics.position[b].copy())
+    for name, rows in zip(names, traj):
+        with open(os.path.join(d_new, name + "_observed.csv"), "w") as f:
+            f.write("x,y,z\n")
+            for r in rows:
+                f.write(",".join(_jl_float(_trunc5(float(c))) for c in r) + "\n")
+    return [nm + ".csv" for nm in names]
+
+
 # ------------------------------------------------------------------ Inference/mcmc.jl
 def gaussian_drift_mcmc(model, gm_args, obs, runs=1000, keep=100, chains=1, args=None):
     """mcmc.jl:53-93: one trace generated from the prior and conditioned on the observations (`generate`, :56), then
