@@ -650,6 +650,93 @@ __device__ __forceinline__ void sphere_solve_two(const f3* nn, const float* dd, 
   w = w + dw;
 }
 
+// The two-contact set a filter run actually meets is the floor plus one wall face (a ball rolling along a wall or
+// wedged in the 1 cm slot under it): n0 = +z and n1 = s e_x or s e_y, whose btPlaneSpace1 tangents are signed unit
+// axes as well (floor: t1 = -e_y, t2 = e_x; wall x: t1 = s e_y, t2 = e_z; wall y: t1 = -s e_x, t2 = e_z).  Every dot
+// product of sphere_solve_two then picks one component, so the same sweep - same rows, order, exit rules - is
+// written on scalars: ~40 % fewer instructions per sweep.  The wall normal is taken as exactly +-1 (the narrow
+// phase normalises it with an approximate reciprocal; the oracle's float64 division gives exactly +-1).
+template <int AX>
+__device__ __forceinline__ void sphere_solve_floor_wall(float s, float d_floor, float d_wall, float restitution, f3& v,
+                                                        f3& w) {
+  const float h = PH_H, c = PH_H * PH_INV_I_SPHERE;
+  const float dinv_t = 1.0f / (PH_INV_M + PH_H * PH_H * PH_INV_I_SPHERE), kt = 1.0f / dinv_t;
+  const float crest = restitution * PH_STATIC_REST;
+  float rhs[2][3], app[2][3];
+#pragma unroll
+  for (int i = 0; i < 2; i++) {
+    float vn, vt1, vt2;
+    if (i == 0) { vn = v.z; vt1 = -v.y - h * w.x; vt2 = v.x - h * w.y; }
+    else if (AX == 0) { vn = s * v.x; vt1 = s * v.y - h * w.z; vt2 = v.z + h * (s * w.y); }
+    else { vn = s * v.y; vt1 = -(s * v.x) - h * w.z; vt2 = v.z - h * (s * w.x); }
+    float rest = 0.f;
+    if (fabsf(vn) >= PH_REST_THRESH) rest = fmaxf(0.f, -crest * vn);
+    const float distance = (i == 0 ? d_floor : d_wall) + PH_SLOP;
+    float verr = rest - vn, perr = 0.f;
+    if (distance > 0.f) verr -= distance / PH_DT;
+    else perr = -distance * PH_ERP / PH_DT;
+    rhs[i][0] = perr + verr;
+    rhs[i][1] = -vt1 * dinv_t;
+    rhs[i][2] = -vt2 * dinv_t;
+    app[i][0] = app[i][1] = app[i][2] = 0.f;
+  }
+  f3 dv = mk3(0.f, 0.f, 0.f), dw = mk3(0.f, 0.f, 0.f);
+  for (int it = 0; it < PH_ITERS; it++) {
+    float resid = 0.f;
+    const f3 pdv = dv, pdw = dw;
+    float dn[2];
+    bool steady = true;
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const float ndv = (i == 0) ? dv.z : s * (AX == 0 ? dv.x : dv.y);
+      float dimp = rhs[i][0] - ndv;
+      const float sum = app[i][0] + dimp;
+      if (sum < 0.f) { dimp = -app[i][0]; app[i][0] = 0.f; steady = false; }
+      else app[i][0] = sum;
+      dn[i] = dimp;
+      if (i == 0) dv.z += dimp;
+      else if (AX == 0) dv.x += s * dimp;
+      else dv.y += s * dimp;
+      resid = fmaxf(resid, dimp * dimp);
+    }
+#pragma unroll
+    for (int i = 0; i < 2; i++) {
+      const float lim = PH_FRICTION * app[i][0];
+      float a1, a2;
+      if (i == 0) { a1 = -dv.y - h * dw.x; a2 = dv.x - h * dw.y; }
+      else if (AX == 0) { a1 = s * dv.y - h * dw.z; a2 = dv.z + h * (s * dw.y); }
+      else { a1 = -(s * dv.x) - h * dw.z; a2 = dv.z - h * (s * dw.x); }
+      float s1 = app[i][1] + (rhs[i][1] - a1 * dinv_t), s2 = app[i][2] + (rhs[i][2] - a2 * dinv_t);
+      const float l2 = s1 * s1 + s2 * s2;
+      if (l2 > lim * lim) {
+        const float scl = lim / sqrtf(l2);
+        s1 *= scl;
+        s2 *= scl;
+        steady = false;
+      }
+      const float d1 = s1 - app[i][1], d2 = s2 - app[i][2];
+      app[i][1] = s1;
+      app[i][2] = s2;
+      if (i == 0) { dv.y -= d1; dv.x += d2; dw.x -= d1 * c; dw.y -= d2 * c; }
+      else if (AX == 0) { dv.y += s * d1; dv.z += d2; dw.y += (s * d2) * c; dw.z -= d1 * c; }
+      else { dv.x -= s * d1; dv.z += d2; dw.x -= (s * d2) * c; dw.z -= d1 * c; }
+      const float e1 = d1 * kt, e2 = d2 * kt;
+      resid = fmaxf(resid, fmaxf(e1 * e1, e2 * e2));
+      const float grow = PH_FRICTION * dn[i];
+      steady = steady && (d1 * d1 + d2 * d2 <= grow * grow);
+    }
+    if (resid <= PH_RESID) break;
+    if (steady) {  // the steady-state exit of sphere_solve_two
+      const f3 ddv = dv - pdv, ddw = dw - pdw;
+      const float mv = fmaxf(fmaxf(fabsf(ddv.x), fabsf(ddv.y)), fabsf(ddv.z));
+      const float mw = fmaxf(fmaxf(fabsf(ddw.x), fabsf(ddw.y)), fabsf(ddw.z)) * PH_H;
+      if (fmaxf(mv, mw) < PH_STALL) break;
+    }
+  }
+  v = v + dv;
+  w = w + dw;
+}
+
 // three or four simultaneous contacts (arena corners): general solver, out of line
 __device__ __noinline__ void sphere_solve_generic(const f3* n, const float* dist, int nc, float restitution, f3* v,
                                                   f3* w) {
@@ -670,8 +757,18 @@ __device__ __noinline__ VelPair sphere_solve_iter(float ceil_half, float restitu
   f3 n[4];
   float dist[4];
   const int nc = sphere_contacts_ordered(sp, x, n, dist);
-  if (nc == 2) sphere_solve_two(n, dist, restitution, v, w);
-  else if (nc > 0) sphere_solve_generic(n, dist, nc, restitution, &v, &w);
+  if (nc == 2) {
+    // floor first (sphere_contacts_ordered), then a wall face: its normal has one non-zero component, x or y.
+    // Which form runs depends on the body's own contacts only, never on its neighbours in the warp: the two forms
+    // agree to rounding, not to the bit (measured: voting on the warp's composition made results lane dependent).
+    const bool floor_wall = n[0].z == 1.0f && n[1].z == 0.f && (n[1].x == 0.f) != (n[1].y == 0.f);
+    if (floor_wall && n[1].y == 0.f)
+      sphere_solve_floor_wall<0>(copysignf(1.0f, n[1].x), dist[0], dist[1], restitution, v, w);
+    else if (floor_wall)
+      sphere_solve_floor_wall<1>(copysignf(1.0f, n[1].y), dist[0], dist[1], restitution, v, w);
+    else
+      sphere_solve_two(n, dist, restitution, v, w);
+  } else if (nc > 0) sphere_solve_generic(n, dist, nc, restitution, &v, &w);
   VelPair r;
   r.v = v;
   r.w = w;
