@@ -2,7 +2,9 @@
 # bench the default library and every smc_physics_b200/libsmcphys_v*.so tuning variant (short run, no ncu)
 mkdir -p gpurun_out
 R=${1:-var}
-true > gpurun_out/pytest_gpu_$R.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/pytest_gpu_$R.log
+if [ -n "${RUN_TESTS:-}" ]; then
+  timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu_$R.log 2>&1; echo "pytest exit $?"; tail -3 gpurun_out/pytest_gpu_$R.log
+fi
 for so in smc_physics_b200/libsmcphys.so smc_physics_b200/libsmcphys_v*.so; do
   [ -f "$so" ] || continue
   echo "== $so"
