@@ -118,8 +118,8 @@ def cpu_leg(args, shape_id, trial, steps, warmup):
 
 def config_of(args, n_gpus):
     return {"workload": "synthetic %s bounce, %d particles/GPU x %d timesteps, rejuvenation_moves=%d, substeps=%d "
-                        "(BASELINE.json configs[3])" % (args.shape, args.particles, args.timesteps, args.moves,
-                                                        args.substeps),
+                        "(BASELINE.json configs[%d])" % (args.shape, args.particles, args.timesteps, args.moves,
+                                                        args.substeps, 3 if args.shape == "sphere" else 4),
             "particles_per_gpu": args.particles, "global_particles": args.particles * n_gpus,
             "timesteps": args.timesteps, "rejuvenation_moves": args.moves, "substeps": args.substeps,
             "shape": args.shape, "sharding": "particles over ranks" if n_gpus > 1 else "single shard",
