@@ -16,6 +16,7 @@ timeout 600 $SHORT > gpurun_out/plain_$R.log 2>&1 &&
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -s 2900 -c 1000 --csv \
     --log-file gpurun_out/launches_$R.csv $SHORT > gpurun_out/ncu_launches_$R.log 2>&1
 echo "launch list exit $?"
+[ -n "${NO_FULL:-}" ] && exit 0   # the full capture then goes in its own call: tools/gpu_ncu.sh <tag>
 timeout 600 $SHORT > gpurun_out/plain2_$R.log 2>&1 &&
 timeout 1500 ncu --set full --clock-control none --import-source on -k regex:k_rejuvenate -s 60 -c 2 \
     -f -o gpurun_out/rejuv_$R $SHORT > gpurun_out/ncu_full_$R.log 2>&1
