@@ -392,13 +392,29 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
   init_body(tp, s);
   double qs = 0.0;
   const float* p = xt + i;
+#ifdef RS_REG_PREFETCH
   float nx = p[0], ny = p[n], nz = p[2 * n];
+#endif
   for (int k = 0; k < steps; k++) {
+#ifdef RS_REG_PREFETCH
     const float x = nx, y = ny, z = nz;
     if (k + 1 < steps) {
       const float* pn = p + (int64_t)(k + 1) * 3 * n;
       nx = pn[0]; ny = pn[n]; nz = pn[2 * n];
     }
+#else
+    // the row of the next step is pulled into L1 now and loaded at the top of the next iteration: held in registers
+    // across the macro step it was spilled right after the load, and the spill store waited for the load
+    // (11 % of the kernel's stall samples, profiles/r01c)
+    const float* pk = p + (int64_t)k * 3 * n;
+    const float x = pk[0], y = pk[n], z = pk[2 * n];
+    if (k + 1 < steps) {
+      const float* pn = pk + 3 * n;
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(pn));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(pn + n));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(pn + 2 * n));
+    }
+#endif
     if (k >= 1) {
       float dx = x - s.x.x, dy = y - s.x.y, dz = z - s.x.z;
       qs += (double)dx * (double)dx + (double)dy * (double)dy + (double)dz * (double)dz;
