@@ -297,91 +297,82 @@ __device__ __forceinline__ void solve_contacts(const Contact* c, int nc, float r
   w = w + dw;
 }
 
-// ---------------------------------------------------------------- cube: plane-manifold contacts in registers
+// ---------------------------------------------------------------- cube: plane-manifold contacts, rows reduced to arms
 // The cube's most common contact set is 1-4 points of the persistent plane manifold and nothing else (resting or
 // tumbling on the floor away from the walls).  All of them share n = +z, t1 = (0,-1,0), t2 = (1,0,0) (btPlaneSpace1
 // of +z), so a row is its arm r alone: r x n = (r.y, -r.x, 0), r x t1 = (r.z, 0, -r.x), r x t2 = (0, r.z, -r.y).
 // Same rows, same sweep order, same exit rule as solve_contacts - the terms multiplied by the zero components of
-// n, t1, t2 are simply not computed - with every row in registers (the general solver indexes 8 x 3 rows of
-// 9 floats in local memory).  Loops are unrolled over the four manifold slots and predicated on nc.
+// n, t1, t2 are simply not computed: 13 floats per contact instead of the general solver's 27, a third of its
+// arithmetic per row.
 struct VelPair { f3 v, w; };
 __device__ __noinline__ VelPair solve_plane_contacts(const Contact* c, int nc, float restitution, f3 v, f3 w) {
   const float inv_m = PH_INV_M, inv_i = PH_INV_I_CUBE;
   const float crest = restitution * PH_STATIC_REST;
-  // slots beyond the largest contact count in the warp are skipped by a uniform branch: nine tenths of the plane
-  // contact sets are a single point (the manifold starts cold at every macro step and gains one point per substep)
-  const int ncw = __reduce_max_sync(__activemask(), nc);
+  // The loops over the manifold slots stay rolled: the kernel is bound by instruction fetch (ncu: no_instruction is
+  // 38 % of its stall samples, at every 128-byte line of straight-line code), and a sweep unrolled over four slots
+  // is 296 instructions against 80 for the rolled pair of loops; the rows then live in local memory (L1 hits).
   f3 r[4];
   float den[4][3], dinv[4][3], rhs[4][3], app[4][3];
+#pragma unroll 1
+  for (int i = 0; i < nc; i++) {
+    r[i] = c[i].r;
+    const float rx2 = r[i].x * r[i].x, ry2 = r[i].y * r[i].y, rz2 = r[i].z * r[i].z;
+    den[i][0] = inv_m + (ry2 + rx2) * inv_i;
+    den[i][1] = inv_m + (rz2 + rx2) * inv_i;
+    den[i][2] = inv_m + (rz2 + ry2) * inv_i;
+    const float relv0 = v.z + (r[i].y * w.x - r[i].x * w.y);
+    const float relv1 = -v.y + (r[i].z * w.x - r[i].x * w.z);
+    const float relv2 = v.x + (r[i].z * w.y - r[i].y * w.z);
+    float rest = 0.f;
+    if (fabsf(relv0) >= PH_REST_THRESH) rest = fmaxf(0.f, -crest * relv0);
+    const float distance = c[i].dist + PH_SLOP;
+    float verr = rest - relv0, perr = 0.f;
+    if (distance > 0.f) verr -= distance / PH_DT;
+    else perr = -distance * PH_ERP / PH_DT;
 #pragma unroll
-  for (int i = 0; i < 4; i++) {
-    if (i >= ncw) break;
-    if (i < nc) {
-      r[i] = c[i].r;
-      const float rx2 = r[i].x * r[i].x, ry2 = r[i].y * r[i].y, rz2 = r[i].z * r[i].z;
-      den[i][0] = inv_m + (ry2 + rx2) * inv_i;
-      den[i][1] = inv_m + (rz2 + rx2) * inv_i;
-      den[i][2] = inv_m + (rz2 + ry2) * inv_i;
-      const float relv0 = v.z + (r[i].y * w.x - r[i].x * w.y);
-      const float relv1 = -v.y + (r[i].z * w.x - r[i].x * w.z);
-      const float relv2 = v.x + (r[i].z * w.y - r[i].y * w.z);
-      float rest = 0.f;
-      if (fabsf(relv0) >= PH_REST_THRESH) rest = fmaxf(0.f, -crest * relv0);
-      const float distance = c[i].dist + PH_SLOP;
-      float verr = rest - relv0, perr = 0.f;
-      if (distance > 0.f) verr -= distance / PH_DT;
-      else perr = -distance * PH_ERP / PH_DT;
-#pragma unroll
-      for (int k = 0; k < 3; k++) { dinv[i][k] = 1.0f / den[i][k]; app[i][k] = 0.f; }
-      rhs[i][0] = (perr + verr) * dinv[i][0];
-      rhs[i][1] = -relv1 * dinv[i][1];
-      rhs[i][2] = -relv2 * dinv[i][2];
-    }
+    for (int k = 0; k < 3; k++) { dinv[i][k] = 1.0f / den[i][k]; app[i][k] = 0.f; }
+    rhs[i][0] = (perr + verr) * dinv[i][0];
+    rhs[i][1] = -relv1 * dinv[i][1];
+    rhs[i][2] = -relv2 * dinv[i][2];
   }
   f3 dv = mk3(0.f, 0.f, 0.f), dw = mk3(0.f, 0.f, 0.f);
   for (int it = 0; it < PH_ITERS; it++) {
     float resid = 0.f;
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-      if (i >= ncw) break;
-      if (i < nc) {
-        float dimp = rhs[i][0] - (dv.z + (r[i].y * dw.x - r[i].x * dw.y)) * dinv[i][0];
-        const float sum = app[i][0] + dimp;
-        if (sum < 0.f) { dimp = -app[i][0]; app[i][0] = 0.f; }
-        else app[i][0] = sum;
-        dv.z += dimp * inv_m;
-        const float q = dimp * inv_i;
-        dw.x += r[i].y * q;
-        dw.y -= r[i].x * q;
-        const float dvel = dimp * den[i][0];
-        resid = fmaxf(resid, dvel * dvel);
-      }
+#pragma unroll 1
+    for (int i = 0; i < nc; i++) {
+      float dimp = rhs[i][0] - (dv.z + (r[i].y * dw.x - r[i].x * dw.y)) * dinv[i][0];
+      const float sum = app[i][0] + dimp;
+      if (sum < 0.f) { dimp = -app[i][0]; app[i][0] = 0.f; }
+      else app[i][0] = sum;
+      dv.z += dimp * inv_m;
+      const float q = dimp * inv_i;
+      dw.x += r[i].y * q;
+      dw.y -= r[i].x * q;
+      const float dvel = dimp * den[i][0];
+      resid = fmaxf(resid, dvel * dvel);
     }
-#pragma unroll
-    for (int i = 0; i < 4; i++) {
-      if (i >= ncw) break;
-      if (i < nc) {
-        const float lim = PH_FRICTION * app[i][0];
-        float s1 = app[i][1] + (rhs[i][1] - (-dv.y + (r[i].z * dw.x - r[i].x * dw.z)) * dinv[i][1]);
-        float s2 = app[i][2] + (rhs[i][2] - (dv.x + (r[i].z * dw.y - r[i].y * dw.z)) * dinv[i][2]);
-        const float l2 = s1 * s1 + s2 * s2;
-        if (l2 > lim * lim) {
-          const float scl = lim / sqrtf(l2);
-          s1 *= scl;
-          s2 *= scl;
-        }
-        const float d1 = s1 - app[i][1], d2 = s2 - app[i][2];
-        app[i][1] = s1;
-        app[i][2] = s2;
-        dv.y -= d1 * inv_m;
-        dv.x += d2 * inv_m;
-        const float q1 = d1 * inv_i, q2 = d2 * inv_i;
-        dw.x += r[i].z * q1;
-        dw.y += r[i].z * q2;
-        dw.z -= r[i].x * q1 + r[i].y * q2;
-        const float e1 = d1 * den[i][1], e2 = d2 * den[i][2];
-        resid = fmaxf(resid, fmaxf(e1 * e1, e2 * e2));
+#pragma unroll 1
+    for (int i = 0; i < nc; i++) {
+      const float lim = PH_FRICTION * app[i][0];
+      float s1 = app[i][1] + (rhs[i][1] - (-dv.y + (r[i].z * dw.x - r[i].x * dw.z)) * dinv[i][1]);
+      float s2 = app[i][2] + (rhs[i][2] - (dv.x + (r[i].z * dw.y - r[i].y * dw.z)) * dinv[i][2]);
+      const float l2 = s1 * s1 + s2 * s2;
+      if (l2 > lim * lim) {
+        const float scl = lim / sqrtf(l2);
+        s1 *= scl;
+        s2 *= scl;
       }
+      const float d1 = s1 - app[i][1], d2 = s2 - app[i][2];
+      app[i][1] = s1;
+      app[i][2] = s2;
+      dv.y -= d1 * inv_m;
+      dv.x += d2 * inv_m;
+      const float q1 = d1 * inv_i, q2 = d2 * inv_i;
+      dw.x += r[i].z * q1;
+      dw.y += r[i].z * q2;
+      dw.z -= r[i].x * q1 + r[i].y * q2;
+      const float e1 = d1 * den[i][1], e2 = d2 * den[i][2];
+      resid = fmaxf(resid, fmaxf(e1 * e1, e2 * e2));
     }
     if (resid <= PH_RESID) break;
   }
