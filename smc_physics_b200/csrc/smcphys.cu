@@ -453,7 +453,9 @@ __device__ __noinline__ ChainOut resimulate_call(float ceil_half, f3 x0, f3 v0, 
 }
 
 #ifndef RJ_MINB_CUBE
-#define RJ_MINB_CUBE 5  // cube: 20 warps at 96 registers (4..7 measured within 5 %)
+#define RJ_MINB_CUBE 8  // cube: 32 warps at 64 registers.  With the contact loops rolled (physics.cuh) the kernel is
+                        // bound by local-memory and arithmetic latency, which warps hide: 4/5/6/7/8 blocks per SM =
+                        // 9.18 / 9.44 / 9.96 / 10.36 / 10.47 M particle-steps/s (2^18 particles)
 #endif
 #ifndef RJ_BLOCK
 #define RJ_BLOCK 128
