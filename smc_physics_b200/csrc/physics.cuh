@@ -233,6 +233,11 @@ __device__ __forceinline__ void plane_space(f3 n, f3& p, f3& q) {
 // One normal row and two friction rows (implicit cone, mu = 0.25) per contact; <= 50 sweeps, normal rows
 // first, early exit when the largest squared velocity change of a sweep is <= 1e-7; no warm starting.
 // Restitution e_body * 0.5 applies only when |v_n| >= 0.2; penetration is recovered at erp 0.08.
+#ifdef PH_ROLL_PGS
+#define PH_PGS_ROLL _Pragma("unroll 1")
+#else
+#define PH_PGS_ROLL
+#endif
 template <int SHAPE>
 __device__ __forceinline__ void solve_contacts(const Contact* c, int nc, float restitution, f3& v, f3& w) {
   const float inv_m = PH_INV_M;
@@ -240,6 +245,7 @@ __device__ __forceinline__ void solve_contacts(const Contact* c, int nc, float r
   const float crest = restitution * PH_STATIC_REST;
   f3 dir[PH_MAXC][3], rxn[PH_MAXC][3];
   float dinv[PH_MAXC][3], rhs[PH_MAXC][3], app[PH_MAXC][3];
+  PH_PGS_ROLL
   for (int i = 0; i < nc; i++) {
     dir[i][0] = c[i].n;
     plane_space(c[i].n, dir[i][1], dir[i][2]);
@@ -264,6 +270,7 @@ __device__ __forceinline__ void solve_contacts(const Contact* c, int nc, float r
   f3 dv = mk3(0.f, 0.f, 0.f), dw = mk3(0.f, 0.f, 0.f);
   for (int it = 0; it < PH_ITERS; it++) {
     float resid = 0.f;
+    PH_PGS_ROLL
     for (int i = 0; i < nc; i++) {
       float dimp = rhs[i][0] - (dot3(dir[i][0], dv) + dot3(rxn[i][0], dw)) * dinv[i][0];
       float sum = app[i][0] + dimp;
@@ -274,6 +281,7 @@ __device__ __forceinline__ void solve_contacts(const Contact* c, int nc, float r
       float dvel = dimp / dinv[i][0];
       resid = fmaxf(resid, dvel * dvel);
     }
+    PH_PGS_ROLL
     for (int i = 0; i < nc; i++) {
       float lim = PH_FRICTION * app[i][0];
       float sm[2];
