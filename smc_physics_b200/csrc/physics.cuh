@@ -323,9 +323,9 @@ struct VelPair { f3 v, w; };
 __device__ __noinline__ VelPair solve_plane_contacts(const Contact* c, int nc, float restitution, f3 v, f3 w) {
   const float inv_m = PH_INV_M, inv_i = PH_INV_I_CUBE;
   const float crest = restitution * PH_STATIC_REST;
-  // The loops over the manifold slots stay rolled: the kernel is bound by instruction fetch (ncu: no_instruction is
-  // 38 % of its stall samples, at every 128-byte line of straight-line code), and a sweep unrolled over four slots
-  // is 296 instructions against 80 for the rolled pair of loops; the rows then live in local memory (L1 hits).
+  // The loops over the manifold slots stay rolled: unrolled over the four slots a sweep is 296 instructions against
+  // 80 for the rolled pair of loops, and the kernel was bound by instruction fetch (ncu: no_instruction 38 % of the
+  // stall samples, one per 128-byte line of straight-line code; 2.5 % rolled).  The rows then live in local memory.
   f3 r[4];
   float den[4][3], dinv[4][3], rhs[4][3], app[4][3];
 #pragma unroll 1
