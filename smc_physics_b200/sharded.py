@@ -158,13 +158,10 @@ class ShardedFilter:
             k_lo, k_hi = ranges[self.rank]
             W_before = sum(W_all[:self.rank])
             my_lo, my_hi = self.rank * self.n, (self.rank + 1) * self.n
-            # offspring that stay on this rank (the bulk: resampling preserves order) are gathered in place ...
+            # only the ranges below / above the own slots travel: chunks for ranks < rank, then ranks > rank.  They are
+            # packed BEFORE the local gather: k_gather resets the log weights of the slots it fills, and pack rebuilds
+            # the integer CDF from the log weights.
             l_lo, l_hi = max(k_lo, my_lo), min(k_hi, my_hi)
-            if l_hi > l_lo:
-                sh.gather_local(t, self._max, W_before, W_total, u0, l_lo, l_hi, l_lo - my_lo)
-            else:
-                sh.gather_local(t, self._max, W_before, W_total, u0, my_lo, my_lo, 0)
-            # ... and only the ranges below / above the own slots travel: chunks for ranks < rank, then ranks > rank
             send[self.rank] = recv[self.rank] = 0
             below, above = (k_lo, min(k_hi, my_lo)), (max(k_lo, my_hi), k_hi)
             n_below = max(0, below[1] - below[0])
@@ -174,6 +171,11 @@ class ShardedFilter:
                 sh.pack(t, self._max, W_before, W_total, u0, below[0], below[1], self.n, sbuf)
             if above[1] > above[0]:
                 sh.pack(t, self._max, W_before, W_total, u0, above[0], above[1], self.n, sbuf[n_below * words:])
+            # offspring that stay on this rank (the bulk: resampling preserves order) are gathered in place
+            if l_hi > l_lo:
+                sh.gather_local(t, self._max, W_before, W_total, u0, l_lo, l_hi, l_lo - my_lo)
+            else:
+                sh.gather_local(t, self._max, W_before, W_total, u0, my_lo, my_lo, 0)
             if G > 1:
                 dist.all_to_all_single(rbuf[:sum(recv) * words], sbuf[:sum(send) * words], [c * words for c in recv],
                                        [c * words for c in send], group=self.group)

@@ -46,8 +46,11 @@ class CpuShard:
     def payload_words(self, t):
         return self.WORDS
 
-    def _ancestors(self, W_before, W_total, u0, k_lo, k_hi):
-        cdf = np.cumsum(self.q, dtype=np.uint64) + np.uint64(W_before)
+    def _ancestors(self, global_max, W_before, W_total, u0, k_lo, k_hi):
+        # like the CUDA phases (k_cdf), the CDF is rebuilt from the CURRENT log weights on every call, so a phase
+        # order that resets log weights before the last pack is caught here too
+        q = orc.weight_q(self.lw, float(global_max[0]))
+        cdf = np.cumsum(q, dtype=np.uint64) + np.uint64(W_before)
         U0 = int(u0 * 4294967296.0)
         tau = np.array([orc.lib().oracle_sys_threshold(U0, k, W_total, self.N) for k in range(k_lo, k_hi)],
                        dtype=np.uint64)
@@ -64,13 +67,14 @@ class CpuShard:
         nxt = self._next()
         cnt = k_hi - k_lo
         if cnt > 0:
-            anc = self._ancestors(W_before, W_total, u0, k_lo, k_hi)
+            anc = self._ancestors(global_max, W_before, W_total, u0, k_lo, k_hi)
             for dst, f in zip(nxt, (self.ident, self.e, self.age)):
                 dst[slot0:slot0 + cnt] = f[anc]
+            self.lw[slot0:slot0 + cnt] = 0.0      # k_gather resets the (single-buffered) log weights of the slots it fills
         self._filled += cnt
 
     def pack(self, t, global_max, W_before, W_total, u0, k_lo, k_hi, spr, send):
-        anc = self._ancestors(W_before, W_total, u0, k_lo, k_hi)
+        anc = self._ancestors(global_max, W_before, W_total, u0, k_lo, k_hi)
         out = send.numpy()
         fields = (self.ident, self.e, self.age)
         pos = 0

@@ -233,23 +233,39 @@ def test_run_smc_small_matches_oracle_draw_for_draw(sp):
     assert np.abs(out["traj"][:, :, same] - ref["traj"][:, :, same]).max() < 1e-4
 
 
+def _t4_compare(sp, shape, R, T, N, seeds, S=5, e_gt=0.7):
+    """GPU posterior (float32 physics) against the FLOAT64 oracle - the reference's arithmetic - at equal N, independent
+    seeds: mean and sd of the elasticity within 3 Monte Carlo standard errors."""
+    path = _truth_path(shape, e_gt, T, S)
+    pfs = []
+    for s in range(seeds):
+        pf = sp.ParticleFilter(num_particles=N, shape=shape, substeps=S, max_timesteps=T, seed=1000 + s)
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        pf.run_smc(R=R, want_stats=False)          # all seeds in flight, one stream each
+        pfs.append(pf)
+    g = [pf.get_particles(want_score=False)["e"] for pf in pfs]
+    for pf in pfs:
+        pf.close()
+    o = [orc.run_smc(shape, N, R, S, INIT_POS, INIT_VEL, path, seed=5000 + s, f32=False, threads=16)["e"]
+         for s in range(seeds)]
+    g_mean, o_mean = np.array([e.mean() for e in g]), np.array([e.mean() for e in o])
+    g_sd, o_sd = np.array([e.std() for e in g]), np.array([e.std() for e in o])
+    se = np.sqrt(g_mean.var(ddof=1) / seeds + o_mean.var(ddof=1) / seeds)
+    se_sd = np.sqrt(g_sd.var(ddof=1) / seeds + o_sd.var(ddof=1) / seeds)
+    print("T4 shape=%d N=%d R=%d T=%d: mean gpu %.4f oracle-f64 %.4f (se %.4f) | sd gpu %.4f oracle %.4f (se %.4f)"
+          % (shape, N, R, T, g_mean.mean(), o_mean.mean(), se, g_sd.mean(), o_sd.mean(), se_sd))
+    assert abs(g_mean.mean() - o_mean.mean()) < 3 * se, (g_mean.mean(), o_mean.mean(), se)
+    assert abs(g_sd.mean() - o_sd.mean()) < 3 * se_sd, (g_sd.mean(), o_sd.mean(), se_sd)
+
+
 @pytest.mark.parametrize("shape,R", [(0, 2), (1, 1)])
 def test_T4_posterior_within_mc_error(sp, shape, R):
-    T, N, seeds = 30, 256, 16
-    path = _truth_path(shape, 0.7, T)
-    g_mean, o_mean, g_sd, o_sd = [], [], [], []
-    for s in range(seeds):
-        with sp.ParticleFilter(num_particles=N, shape=shape, substeps=5, max_timesteps=T, seed=1000 + s) as pf:
-            pf.set_trial(INIT_POS, INIT_VEL, path)
-            pf.run_smc(R=R, want_stats=False)
-            e = pf.get_particles(want_score=False)["e"]
-        ref = orc.run_smc(shape, N, R, 5, INIT_POS, INIT_VEL, path, seed=5000 + s, f32=True, threads=8)["e"]
-        g_mean.append(e.mean()); o_mean.append(ref.mean()); g_sd.append(e.std()); o_sd.append(ref.std())
-    g_mean, o_mean, g_sd, o_sd = map(np.asarray, (g_mean, o_mean, g_sd, o_sd))
-    se = np.sqrt(g_mean.var(ddof=1) / seeds + o_mean.var(ddof=1) / seeds)
-    assert abs(g_mean.mean() - o_mean.mean()) < 3 * se + 1e-3, (g_mean.mean(), o_mean.mean(), se)
-    se_sd = np.sqrt(g_sd.var(ddof=1) / seeds + o_sd.var(ddof=1) / seeds)
-    assert abs(g_sd.mean() - o_sd.mean()) < 3 * se_sd + 1e-3, (g_sd.mean(), o_sd.mean(), se_sd)
+    _t4_compare(sp, shape, R, T=30, N=256, seeds=32)
+
+
+def test_T4_posterior_config1_shape(sp):
+    """BASELINE.json configs[1]: cube, 1000 particles, R = 5, 120 frames, S = 5."""
+    _t4_compare(sp, 1, 5, T=120, N=1000, seeds=32)
 
 
 def test_score_and_states_are_consistent(sp):
