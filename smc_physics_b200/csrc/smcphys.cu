@@ -18,6 +18,7 @@
 #include <vector>
 
 #include "../../include/smcphys.h"
+#include "nccl_dl.h"
 #include "physics.cuh"
 #include "rng.cuh"
 
@@ -56,6 +57,19 @@ struct Ctl {
   int cur;            // buffer holding the particles
   int resampled;      // decision of the current step
   int pad;
+  // sharded filter: written by k_decide from the all-gathered sums, identical decisions on every rank
+  u64 W_before, W_total;  // integer weight of all lower ranks / of all ranks
+  u64 U0;                 // uniform offset of this step's systematic resampling, 32-bit fixed point
+  long long k_lo, k_hi;   // global slots [k_lo, k_hi) filled by the offspring of this shard's particles
+};
+
+// device-visible buffers of one rank of a sharded filter (own pointers, peer-mapped or IPC-opened ones)
+struct Peer {
+  float* xt[2];
+  float* st[2];
+  double* e[2];
+  double* qs[2];
+  u64* cdf;
 };
 
 struct TrialPar {
@@ -293,8 +307,9 @@ __global__ void __launch_bounds__(TILE_THREADS) k_weight_sums(Bufs B, Ctl* ctl, 
 // C_i = W_before + inclusive prefix sum of q.  Skipped when the step does not resample (gate != 0 reads the
 // device decision).
 __global__ void __launch_bounds__(TILE_THREADS) k_cdf(Bufs B, const Ctl* ctl, const double* gmax_ptr, int64_t n,
-                                                      u64 W_before, int gate) {
+                                                      u64 W_before, int gate, const u64* W_before_ptr = nullptr) {
   if (gate && !ctl->resampled) return;
+  if (W_before_ptr) W_before = *W_before_ptr;
   __shared__ u64 wtot[TILE_THREADS / 32];
   const double gmax = *gmax_ptr;
   // blocked arrangement: thread owns TILE_ITEMS consecutive particles
@@ -391,39 +406,30 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
                                              float* traj) {
   init_body(tp, s);
   double qs = 0.0;
-  const float* p = xt + i;
-#ifdef RS_REG_PREFETCH
-  float nx = p[0], ny = p[n], nz = p[2 * n];
-#endif
-  for (int k = 0; k < steps; k++) {
-#ifdef RS_REG_PREFETCH
-    const float x = nx, y = ny, z = nz;
-    if (k + 1 < steps) {
-      const float* pn = p + (int64_t)(k + 1) * 3 * n;
-      nx = pn[0]; ny = pn[n]; nz = pn[2 * n];
-    }
-#else
-    // the row of the next step is pulled into L1 now and loaded at the top of the next iteration: held in registers
-    // across the macro step it was spilled right after the load, and the spill store waited for the load
-    // (11 % of the kernel's stall samples, profiles/r01c)
-    const float* pk = p + (int64_t)k * 3 * n;
+  // one pointer walks the rows (3 n floats apart); the row of the next step is pulled into L1 while the current macro
+  // step runs and is loaded at the top of the next iteration (held in registers across the macro step it was spilled
+  // right after the load, and the spill store waited for the load: 11 % of the stall samples, profiles/r01c)
+  const float* pk = xt + i;
+  float* o = TRAJ ? traj + i : nullptr;
+  const int64_t row = 3 * n;
+#pragma unroll 1
+  for (int k = steps; k > 0; k--) {
     const float x = pk[0], y = pk[n], z = pk[2 * n];
-    if (k + 1 < steps) {
-      const float* pn = pk + 3 * n;
-      asm volatile("prefetch.global.L1 [%0];" ::"l"(pn));
-      asm volatile("prefetch.global.L1 [%0];" ::"l"(pn + n));
-      asm volatile("prefetch.global.L1 [%0];" ::"l"(pn + 2 * n));
+    pk += row;
+    if (k > 1) {
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(pk));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(pk + n));
+      asm volatile("prefetch.global.L1 [%0];" ::"l"(pk + 2 * n));
     }
-#endif
-    if (k >= 1) {
+    if (k != steps) {
       float dx = x - s.x.x, dy = y - s.x.y, dz = z - s.x.z;
       qs += (double)dx * (double)dx + (double)dy * (double)dy + (double)dz * (double)dz;
     }
     s.x = mk3(x, y, z);
     macro_step<SHAPE, TRACK_Q>(sp, e, S, s);
     if (TRAJ) {
-      float* o = traj + (int64_t)k * 3 * n + i;
       o[0] = s.x.x; o[n] = s.x.y; o[2 * n] = s.x.z;
+      o += row;
     }
   }
   return qs;
@@ -440,13 +446,53 @@ struct ChainOut {
 template <int SHAPE>
 __device__ __noinline__ ChainOut resimulate_call(float ceil_half, f3 x0, f3 v0, int S, float e,
                                                  const float* __restrict__ xt, int64_t n, int64_t i, int steps) {
+  ChainOut o;
+  if (SHAPE == SHAPE_SPHERE) {
+    // the sphere chain on one struct of loop state (physics.cuh, SphereChain): rows walked by one pointer, the row of
+    // the next step loaded while the current macro step runs (the loop itself needs ~30 registers, so holding the row
+    // costs nothing; an L1 prefetch instead left the load of the row as the top stall of the loop)
+    SphereChain c;
+    c.v = v0; c.w = mk3(0.f, 0.f, 0.f);
+    c.restitution = e; c.ceil_half = ceil_half;
+    c.pk = xt + i; c.n = n; c.qs = 0.0; c.S = S;
+    c.x = x0;
+    c.nx = x0;
+    if (steps > 0) {
+      c.x = mk3(c.pk[0], c.pk[c.n], c.pk[2 * c.n]);
+#pragma unroll 1
+      for (c.k = steps; ; ) {
+        c.pk += 3 * c.n;
+#ifdef RS_L1_PREFETCH
+        if (c.k > 1) {
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(c.pk));
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(c.pk + c.n));
+          asm volatile("prefetch.global.L1 [%0];" ::"l"(c.pk + 2 * c.n));
+        }
+#else
+        if (c.k > 1) c.nx = mk3(c.pk[0], c.pk[c.n], c.pk[2 * c.n]);
+#endif
+#pragma unroll 1
+        for (c.sub = c.S; c.sub > 0; c.sub--) sphere_chain_substep(c);
+        if (--c.k == 0) break;
+#ifdef RS_L1_PREFETCH
+        c.nx = mk3(c.pk[0], c.pk[c.n], c.pk[2 * c.n]);
+#endif
+        const float dx = c.nx.x - c.x.x, dy = c.nx.y - c.x.y, dz = c.nx.z - c.x.z;
+        c.qs += (double)dx * (double)dx + (double)dy * (double)dy + (double)dz * (double)dz;
+        c.x = c.nx;
+      }
+    }
+    o.qs = c.qs;
+    o.x = c.x; o.v = c.v; o.w = c.w;
+    o.q.x = o.q.y = o.q.z = 0.f; o.q.w = 1.f;
+    return o;
+  }
   ScenePar sp;
   sp.ceil_half = ceil_half;
   TrialPar tp;
   tp.x0[0] = x0.x; tp.x0[1] = x0.y; tp.x0[2] = x0.z;
   tp.v0[0] = v0.x; tp.v0[1] = v0.y; tp.v0[2] = v0.z;
   Body s;
-  ChainOut o;
   o.qs = resimulate<SHAPE, SHAPE == SHAPE_CUBE, false>(sp, tp, S, e, xt, n, i, steps, s, nullptr);
   o.x = s.x; o.v = s.v; o.w = s.w; o.q = s.q;
   return o;
