@@ -21,6 +21,11 @@ extern "C" {
 #define SMCPHYS_ESTATE (-3) /* call out of order (e.g. run before set_trial) */
 #define SMCPHYS_ENOMEM (-4)
 
+#define SMCPHYS_RESAMPLE_SYSTEMATIC 0
+#define SMCPHYS_RESAMPLE_MULTINOMIAL 1
+#define SMCPHYS_MAX_RANKS 64 /* shards of one filter */
+#define SMCPHYS_UNIQUE_ID_BYTES 128
+
 #define SMCPHYS_SPHERE 0 /* Model/bouncing_object.jl:71  sphere r = 0.05 */
 #define SMCPHYS_CUBE 1   /* Model/bouncing_object.jl:68  box half extent 0.05 */
 
@@ -46,6 +51,9 @@ typedef struct smcphys_config {
   double ceiling_half;        /* 0.01 */
   int64_t ess_num, ess_den;   /* resample when ESS < N * ess_num / ess_den (1/2) */
   uint64_t seed;
+  int32_t resampler;          /* SMCPHYS_RESAMPLE_SYSTEMATIC (north_star) | SMCPHYS_RESAMPLE_MULTINOMIAL (what
+                                 Gen.maybe_resample! draws in Gen 0.4.7, Inference/particle_filter.jl:55) */
+  int32_t pad_;
 } smcphys_config;
 
 /* per PF step diagnostics (the reference discards its own @elapsed, particle_filter.jl:49,75) */
@@ -88,6 +96,28 @@ int smcphys_get_log_ml(smcphys_handle* h, double* log_ml);
 /* predict (particle_filter.jl:84-102): roll every final particle forward n_steps with sampled transition and
  * observation noise; out layouts [n_steps][3][num_particles] float32 (either may be NULL). */
 int smcphys_predict(smcphys_handle* h, int32_t n_steps, float* pos_out, float* obs_out);
+
+/* ---- one filter over several GPUs, inside the library (the multi-GPU drop-in for main.jl:5-9,54: the host makes
+ * the same set_trial / run_smc / get_particles calls, the particles of a trial are sharded over the GPUs).
+ * Per PF step, all stream ordered with no host synchronisation: local max -> all-reduce(max) -> integer weight sums
+ * -> all-gather -> ESS decision, CDF offset and offspring slot range on the device -> ancestors -> the offspring are
+ * STORED into the destination rank's idle buffers through peer memory (NVLink) -> barrier -> rejuvenation.
+ *
+ * (a) One process per GPU (torchrun, MPI, Julia Distributed workers): every rank creates its handle with
+ *     num_particles = N / nranks, global_particles = N, particle_offset = rank * num_particles, rank 0 calls
+ *     smcphys_comm_unique_id and ships the 128 bytes to the others (any transport), every rank calls
+ *     smcphys_comm_init_rank (NCCL communicator + CUDA IPC mapping of the peers' buffers).  smcphys_run_smc is then
+ *     collective: every rank calls it.  NCCL is bound at run time (dlopen libnccl.so.2).
+ * (b) One process, several devices (a single ccall-ing Julia process): smcphys_create_multi returns ONE handle that
+ *     owns a shard per listed device (cfg->num_particles particles each; a device may be listed more than once);
+ *     set_trial / run_smc / get_particles / get_log_ml / synchronize / destroy act on the whole filter. */
+int smcphys_comm_unique_id(uint8_t id[SMCPHYS_UNIQUE_ID_BYTES]);
+int smcphys_comm_init_rank(smcphys_handle* h, const uint8_t id[SMCPHYS_UNIQUE_ID_BYTES], int32_t nranks, int32_t rank);
+int smcphys_create_multi(const smcphys_config* cfg, int32_t n_shards, const int32_t* devices, smcphys_handle** out);
+/* particles of all shards of a smcphys_create_multi handle (= num_particles of an ordinary handle) */
+int64_t smcphys_total_particles(smcphys_handle* h);
+/* simulator outputs of the first `steps` PF steps actually applied (the `traj` rows smcphys_get_particles writes) */
+int32_t smcphys_steps_done(smcphys_handle* h);
 
 /* ---- the same filter as phases, for particles sharded over several handles / GPUs (one per process).  The
  * host does the exchanges between phases (NCCL through torch.distributed or ccall'd NCCL).  Pointers named

@@ -22,6 +22,7 @@ class Config(C.Structure):
         ("max_timesteps", C.c_int32), ("rejuvenation_moves", C.c_int32),
         ("observation_noise", C.c_double), ("transition_noise", C.c_double), ("proposal_sigma", C.c_double),
         ("ceiling_half", C.c_double), ("ess_num", C.c_int64), ("ess_den", C.c_int64), ("seed", C.c_uint64),
+        ("resampler", C.c_int32), ("pad_", C.c_int32),
     ]
 
 
@@ -41,6 +42,11 @@ SIGNATURES = {
     "smcphys_device_count": (C.c_int, []),
     "smcphys_launch_count": (C.c_int64, []),
     "smcphys_create": (C.c_int, [C.POINTER(Config), C.POINTER(_H)]),
+    "smcphys_create_multi": (C.c_int, [C.POINTER(Config), C.c_int32, C.POINTER(C.c_int32), C.POINTER(_H)]),
+    "smcphys_comm_unique_id": (C.c_int, [C.c_char_p]),
+    "smcphys_comm_init_rank": (C.c_int, [_H, C.c_char_p, C.c_int32, C.c_int32]),
+    "smcphys_total_particles": (C.c_int64, [_H]),
+    "smcphys_steps_done": (C.c_int32, [_H]),
     "smcphys_destroy": (C.c_int, [_H]),
     "smcphys_set_stream": (C.c_int, [_H, C.c_void_p]),
     "smcphys_set_trial": (C.c_int, [_H, _dp, _dp, _dp, C.c_int32]),

@@ -87,14 +87,35 @@ def default_config(**kw):
     return cfg
 
 
-class ParticleFilter:
-    """One smcphys handle: the per-trial filter state run_inference.jl:33-48 sets up."""
+SYSTEMATIC, MULTINOMIAL = 0, 1
 
-    def __init__(self, **cfg):
+
+class ParticleFilter:
+    """One smcphys handle: the per-trial filter state run_inference.jl:33-48 sets up.
+
+    devices=[d0, d1, ...] makes it ONE filter sharded over several devices of this process (smcphys_create_multi,
+    num_particles per device); comm_init() joins the handles of several processes into one filter (NCCL)."""
+
+    def __init__(self, devices=None, **cfg):
         self.cfg = default_config(**cfg)
         self._h = _lib._H()
-        check(lib().smcphys_create(C.byref(self.cfg), C.byref(self._h)))
+        if devices is None:
+            check(lib().smcphys_create(C.byref(self.cfg), C.byref(self._h)))
+        else:
+            devs = (C.c_int32 * len(devices))(*[int(d) for d in devices])
+            check(lib().smcphys_create_multi(C.byref(self.cfg), len(devices), devs, C.byref(self._h)))
         self.T = 0
+
+    @staticmethod
+    def comm_unique_id():
+        """128 bytes that rank 0 makes and ships to the other ranks (any transport) before comm_init."""
+        buf = C.create_string_buffer(128)
+        check(lib().smcphys_comm_unique_id(buf))
+        return buf.raw
+
+    def comm_init(self, unique_id, nranks, rank):
+        """Collective: NCCL communicator + CUDA IPC mapping of the peers' buffers; run_smc is collective afterwards."""
+        check(lib().smcphys_comm_init_rank(self._h, C.create_string_buffer(bytes(unique_id), 128), nranks, rank))
 
     def close(self):
         if getattr(self, "_h", None):
@@ -111,7 +132,7 @@ class ParticleFilter:
 
     @property
     def n(self):
-        return int(self.cfg.num_particles)
+        return int(lib().smcphys_total_particles(self._h))
 
     def set_stream(self, cuda_stream_ptr):
         check(lib().smcphys_set_stream(self._h, C.c_void_p(cuda_stream_ptr)))
@@ -144,7 +165,10 @@ class ParticleFilter:
         check(lib().smcphys_synchronize(self._h))
 
     def get_particles(self, want_score=True, want_traj=False, steps=None):
-        n, T = self.n, self.T if steps is None else steps
+        # the library writes one trajectory row per PF step applied so far; `steps` is kept for the callers' sake
+        n, T = self.n, int(lib().smcphys_steps_done(self._h))
+        if steps is not None and steps != T:
+            raise ValueError("get_particles(steps=%d): the filter has applied %d steps" % (steps, T))
         e, lw = np.zeros(n), np.zeros(n)
         score = np.zeros(n) if want_score else None
         traj = np.zeros((T, 3, n), F32) if want_traj else None

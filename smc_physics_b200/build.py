@@ -7,13 +7,13 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "libsmcphys.so")
 SOURCES = ["smcphys.cu"]
-DEPS = ["smcphys.cu", "physics.cuh", "rng.cuh", os.path.join("..", "..", "include", "smcphys.h")]
+DEPS = ["smcphys.cu", "physics.cuh", "rng.cuh", "nccl_dl.h", os.path.join("..", "..", "include", "smcphys.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
     # approximate sqrt / division (MUFU) and flush-to-zero in the float32 physics; sin/cos/log stay accurate
     "-prec-sqrt=false", "-prec-div=false", "-ftz=true",
-    "--shared", "-Xcompiler", "-fPIC",
+    "--shared", "-Xcompiler", "-fPIC", "-ldl",
 ]
 
 

@@ -13,7 +13,7 @@
 
 namespace smcphys {
 
-enum { ST_PRIOR = 0, ST_TRANSITION = 1, ST_PROPOSAL = 2, ST_RESAMPLE = 3, ST_PREDICT = 4 };
+enum { ST_PRIOR = 0, ST_TRANSITION = 1, ST_PROPOSAL = 2, ST_RESAMPLE = 3, ST_PREDICT = 4, ST_RESAMPLE_MULTI = 5, ST_MCMC = 6 };
 
 __host__ __device__ __forceinline__ void philox4x32_10(uint64_t seed, uint32_t c0, uint32_t c1, uint32_t c2,
                                                         uint32_t c3, uint32_t out[4]) {
@@ -141,6 +141,11 @@ __host__ __device__ __forceinline__ uint64_t sys_threshold(uint64_t U0, uint64_t
   unsigned __int128 P = (unsigned __int128)(U0 + (k << 32)) * W;
   P >>= 32;
   return (uint64_t)(P / N);
+}
+
+// multinomial threshold: floor(u W / 2^64) for 64 uniform bits u
+__host__ __device__ __forceinline__ uint64_t multi_threshold(uint64_t u, uint64_t W) {
+  return (uint64_t)(((unsigned __int128)u * W) >> 64);
 }
 
 }  // namespace smcphys

@@ -61,6 +61,7 @@ struct Ctl {
   u64 W_before, W_total;  // integer weight of all lower ranks / of all ranks
   u64 U0;                 // uniform offset of this step's systematic resampling, 32-bit fixed point
   long long k_lo, k_hi;   // global slots [k_lo, k_hi) filled by the offspring of this shard's particles
+  double lmax;            // this shard's largest log weight, read by the other shards of a one-process group
 };
 
 // device-visible buffers of one rank of a sharded filter (own pointers, peer-mapped or IPC-opened ones)
@@ -70,6 +71,8 @@ struct Peer {
   double* e[2];
   double* qs[2];
   u64* cdf;
+  struct Ctl* ctl;
+  u64* sums;  // W, S1, S2 of that rank (k_weight_sums)
 };
 
 struct TrialPar {
@@ -734,6 +737,133 @@ __global__ void k_unpack(Bufs B, const Ctl* ctl, int64_t n, const float* chunk, 
 }
 __global__ void k_set_resampled(Ctl* ctl, int v) { ctl->resampled = v; }
 
+// ---------------------------------------------------------------- sharded filter, decided and exchanged on the device
+// #{k in [0,N) : tau_k < C}; tau is non-decreasing in k
+__host__ __device__ static inline int64_t count_below(u64 C, u64 U0, u64 W, int64_t N) {
+  int64_t lo = 0, hi = N;  // first k with tau_k >= C
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (sys_threshold(U0, (u64)mid, W, (u64)N) < C) lo = mid + 1; else hi = mid;
+  }
+  return lo;
+}
+
+// One thread: from the all-gathered integer sums (W, S1, S2 of every rank) take the ESS decision of
+// Gen.maybe_resample! (Inference/particle_filter.jl:55) - identical on every rank, integers - and derive this rank's
+// CDF offset and the global slot range its offspring fill (systematic resampling preserves order).
+__global__ void k_decide(Ctl* ctl, const u64* all, const Peer* peers, int G, int rank, int64_t N, int64_t ess_num,
+                         int64_t ess_den, u64 U0, int t, double* st_ess, double* st_lse, int* st_res) {
+  u64 W = 0, S1 = 0, S2 = 0, Wb = 0, Wl = 0;
+  for (int r = 0; r < G; r++) {
+    // NCCL all-gather result, or (one-process group) the other shards' sums through peer memory
+    const volatile u64* q = all ? all + 3 * r : peers[r].sums;
+    const u64 w = q[0];
+    if (r < rank) Wb += w;
+    if (r == rank) Wl = w;
+    W += w; S1 += q[1]; S2 += q[2];
+  }
+  unsigned __int128 lhs = (unsigned __int128)S1 * S1 * (u64)ess_den;
+  unsigned __int128 rhs = (unsigned __int128)S2 * (u64)N * (u64)ess_num;
+  const int res = lhs < rhs;
+  const double lse = ctl->gmax + log((double)W / 549755813888.0);
+  ctl->resampled = res;
+  if (res) ctl->log_ml += lse - log((double)N);
+  ctl->W_before = Wb; ctl->W_total = W; ctl->U0 = U0;
+  ctl->k_lo = res ? count_below(Wb, U0, W, N) : 0;
+  ctl->k_hi = res ? count_below(Wb + Wl, U0, W, N) : 0;
+  if (st_ess) {
+    st_ess[t] = S2 ? ((double)S1 * (double)S1) / (double)S2 : 0.0;
+    st_lse[t] = lse;
+    st_res[t] = res;
+  }
+}
+
+// one-process group: global max of the shards' local maxima through peer memory (stands in for the NCCL all-reduce)
+__global__ void k_copy_lmax(Ctl* ctl) { ctl->lmax = ctl->gmax; }
+__global__ void k_local_max(Ctl* ctl, const Peer* peers, int G) {
+  double m = -INFINITY;
+  for (int r = 0; r < G; r++) m = fmax(m, ((const volatile Ctl*)peers[r].ctl)->lmax);
+  ctl->gmax = m;
+}
+
+// ancestors of the offspring k_lo + j, j < k_hi - k_lo, in this shard's CDF (which starts at W_before).  A shard's
+// offspring can outnumber its particles (up to N): grid-stride over j, the grid is sized for the usual count ~ n.
+__global__ void k_index_sh(Bufs B, const Ctl* ctl, int64_t n, int64_t Nglob) {
+  if (!ctl->resampled) return;
+  const int64_t k_lo = ctl->k_lo, count = ctl->k_hi - k_lo;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < count; j += (int64_t)gridDim.x * blockDim.x) {
+    const u64 tau = sys_threshold(ctl->U0, (u64)(k_lo + j), ctl->W_total, (u64)Nglob);
+    int64_t lo = 0, hi = n - 1;
+    while (lo < hi) {
+      int64_t mid = (lo + hi) >> 1;
+      if (B.cdf[mid] > tau) hi = mid; else lo = mid + 1;
+    }
+    B.idx[j] = (int)lo;
+  }
+}
+
+// Offspring k_lo + j of this shard goes to global slot K = k_lo + j = rank d = K / n, local slot K - d n: stored
+// straight into that rank's idle buffers through peer memory (NVLink stores; the own rank is just another entry of
+// the table).  Consecutive offspring go to consecutive slots, so a warp writes 128 consecutive bytes per row.
+__global__ void k_push(Bufs B, const Ctl* ctl, const Peer* __restrict__ peers, int64_t n) {
+  if (!ctl->resampled) return;
+  const int64_t k_lo = ctl->k_lo, count = ctl->k_hi - k_lo;
+  const int cur = ctl->cur, nxt = cur ^ 1;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < count; j += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t K = k_lo + j, d = K / n, k = K - d * n, a = B.idx[j];
+    const Peer P = peers[d];
+    P.e[nxt][k] = B.e[cur][a];
+    P.qs[nxt][k] = B.qs[cur][a];
+#pragma unroll
+    for (int c = 0; c < 13; c++) P.st[nxt][c * n + k] = B.st[cur][c * n + a];
+  }
+}
+__global__ void __launch_bounds__(256) k_push_hist(Bufs B, const Ctl* ctl, const Peer* __restrict__ peers, int64_t n,
+                                                   int rows) {
+  if (!ctl->resampled) return;
+  const int64_t k_lo = ctl->k_lo, count = ctl->k_hi - k_lo;
+  const int cur = ctl->cur, nxt = cur ^ 1;
+  const int c0 = (int)blockIdx.y * (GH_ROWS * 3), c1 = rows * 3;
+  for (int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; j < count; j += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t K = k_lo + j, d = K / n, k = K - d * n, a = B.idx[j];
+    const float* __restrict__ src = B.xt[cur] + (int64_t)c0 * n + a;
+    float* __restrict__ dst = peers[d].xt[nxt] + (int64_t)c0 * n + k;
+    float v[GH_ROWS * 3];
+#pragma unroll
+    for (int c = 0; c < GH_ROWS * 3; c++)
+      if (c0 + c < c1) v[c] = __ldg(src + (int64_t)c * n);
+#pragma unroll
+    for (int c = 0; c < GH_ROWS * 3; c++)
+      if (c0 + c < c1) dst[(int64_t)c * n] = v[c];
+  }
+}
+// after the exchange: log weights := 0 (Gen.maybe_resample!).  Runs after the barrier that follows the pushes; the
+// log weights are single buffered and a rank's CDF is built from them, so nobody may reset them earlier.
+__global__ void k_post_resample(Bufs B, const Ctl* ctl, int64_t n) {
+  if (!ctl->resampled) return;
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) B.logw[i] = 0.0;
+}
+
+// Multinomial parents (what Gen.maybe_resample! draws in Gen 0.4.7: rand(Categorical(w)) per slot): slot k takes
+// tau_k = floor(u_k W / 2^64) with u_k 64 Philox bits of counter (global slot, step), against the same integer CDF.
+__global__ void k_index_multi(Bufs B, const Ctl* ctl, int64_t n, const u64* W_ptr, u64 seed, int t, int64_t goff,
+                              int64_t count, int gate) {
+  if (gate && !ctl->resampled) return;
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= count) return;
+  uint32_t r[4];
+  philox4x32_10(seed, (uint32_t)(goff + j), (uint32_t)t, 0u, (uint32_t)ST_RESAMPLE_MULTI, r);
+  const u64 u = ((u64)r[0] << 32) | (u64)r[1];
+  const u64 tau = multi_threshold(u, *W_ptr);
+  int64_t lo = 0, hi = n - 1;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (B.cdf[mid] > tau) hi = mid; else lo = mid + 1;
+  }
+  B.idx[j] = (int)lo;
+}
+
 // FP32 FMA peak probe: the roofline denominator of the simulate kernels (not in MEASURED_PEAKS.json)
 __global__ void __launch_bounds__(256) k_fma_peak(float* out, int iters, float a, float b) {
   float x[8];
@@ -769,6 +899,16 @@ struct smcphys_handle {
   int ntiles = 0;
   int64_t local_gathered = 0;  // slots of the current resampling step already filled by pf_gather_local
   std::vector<void*> allocs;
+  // sharded filter inside the library: NCCL communicator (one process per GPU) or a one-process group of shards
+  ncclComm_t comm = nullptr;
+  int nranks = 1, rank = 0;
+  Peer* d_peers = nullptr;          // device table, nranks entries
+  u64 *d_sums3 = nullptr, *d_all = nullptr;
+  int* d_bar = nullptr;
+  std::vector<void*> ipc_opened;    // peer buffers opened with cudaIpcOpenMemHandle
+  std::vector<smcphys_handle*> kids;  // group handle: the shards it owns (smcphys_create_multi)
+  smcphys_handle* parent = nullptr;
+  cudaEvent_t ev_sync = nullptr;    // one-process group: this shard's progress marker
   bool prof = false;
   struct Ev { int cls; cudaEvent_t a, b; };
   std::vector<Ev> evs;
@@ -794,6 +934,18 @@ struct ProfScope {
 };
 
 static inline unsigned int nblk(int64_t n, int b) { return (unsigned int)((n + b - 1) / b); }
+
+struct DevScratch {  // device scratch that frees on scope exit (also on the early returns of CK / LAUNCH)
+  std::vector<void*> p;
+  ~DevScratch() { for (void* q : p) cudaFree(q); }
+  template <class T> cudaError_t get(T** out, size_t count) {
+    void* q = nullptr;
+    cudaError_t e = cudaMalloc(&q, count * sizeof(T) + 16);
+    if (e == cudaSuccess) p.push_back(q);
+    *out = (T*)q;
+    return e;
+  }
+};
 
 template <class T>
 static int dalloc(smcphys_handle* h, T** p, size_t count) {
@@ -833,6 +985,7 @@ int smcphys_config_default(smcphys_config* c) {
   c->ceiling_half = 0.01;                 // bouncing_object.jl:53
   c->ess_num = 1; c->ess_den = 2;         // particle_filter.jl:55
   c->seed = 1234;
+  c->resampler = SMCPHYS_RESAMPLE_SYSTEMATIC;  // north_star; SMCPHYS_RESAMPLE_MULTINOMIAL = Gen.maybe_resample!
   return 0;
 }
 
@@ -850,6 +1003,8 @@ int smcphys_create(const smcphys_config* cfg, smcphys_handle** out) {
   if (!(cfg->observation_noise > 0) || !(cfg->transition_noise > 0) || !(cfg->proposal_sigma > 0))
     return fail(SMCPHYS_EINVAL, "noise parameters must be positive");
   if (cfg->ess_num < 0 || cfg->ess_den < 1) return fail(SMCPHYS_EINVAL, "bad ESS fraction");
+  if (cfg->resampler != SMCPHYS_RESAMPLE_SYSTEMATIC && cfg->resampler != SMCPHYS_RESAMPLE_MULTINOMIAL)
+    return fail(SMCPHYS_EINVAL, "resampler must be 0 (systematic) or 1 (multinomial)");
   int ndev = smcphys_device_count();
   if (ndev <= 0) return fail(SMCPHYS_ECUDA, "no CUDA device (libsmcphys has no CPU path)");
   if (cfg->device < 0 || cfg->device >= ndev) return fail(SMCPHYS_EINVAL, "device ordinal out of range");
@@ -871,8 +1026,16 @@ int smcphys_create(const smcphys_config* cfg, smcphys_handle** out) {
   rc = rc ? rc : dalloc(h, &h->B.cdf, (size_t)n);
   rc = rc ? rc : dalloc(h, &h->B.tile_sum, (size_t)h->ntiles);
   rc = rc ? rc : dalloc(h, &h->B.tile_off, (size_t)h->ntiles);
-  rc = rc ? rc : dalloc(h, &h->B.idx, (size_t)n);
+  const bool sharded = cfg->global_particles > cfg->num_particles;
+  // a shard's offspring can outnumber its particles (up to N): the ancestor scratch holds N entries when sharded
+  rc = rc ? rc : dalloc(h, &h->B.idx, (size_t)(sharded ? cfg->global_particles : n));
   rc = rc ? rc : dalloc(h, &h->ctl, 1);
+  rc = rc ? rc : dalloc(h, &h->d_sums3, (size_t)4);
+  if (sharded) {
+    rc = rc ? rc : dalloc(h, &h->d_peers, (size_t)SMCPHYS_MAX_RANKS);
+    rc = rc ? rc : dalloc(h, &h->d_all, (size_t)3 * SMCPHYS_MAX_RANKS);
+    rc = rc ? rc : dalloc(h, &h->d_bar, (size_t)4);
+  }
   rc = rc ? rc : dalloc(h, &h->d_obs, Tm * 3);
   rc = rc ? rc : dalloc(h, &h->d_ess, Tm);
   rc = rc ? rc : dalloc(h, &h->d_lse, Tm);
@@ -885,13 +1048,24 @@ int smcphys_create(const smcphys_config* cfg, smcphys_handle** out) {
   }
   h->own_stream = true;
   cudaMemsetAsync(h->ctl, 0, sizeof(Ctl), h->stream);
+  if (sharded) cudaMemsetAsync(h->d_bar, 0, sizeof(int) * 4, h->stream);
   *out = h;
   return 0;
 }
 
 int smcphys_destroy(smcphys_handle* h) {
   if (!h) return 0;
+  if (!h->kids.empty()) {
+    for (auto* k : h->kids) smcphys_synchronize(k);
+    for (auto* k : h->kids) { k->parent = nullptr; smcphys_destroy(k); }
+    delete h;
+    return 0;
+  }
   cudaSetDevice(h->cfg.device);
+  if (h->stream) cudaStreamSynchronize(h->stream);
+  if (h->comm && nccl().lib) nccl().CommDestroy(h->comm);
+  for (void* p : h->ipc_opened) cudaIpcCloseMemHandle(p);
+  if (h->ev_sync) cudaEventDestroy(h->ev_sync);
   if (h->stream) cudaStreamSynchronize(h->stream);
   for (void* p : h->allocs) cudaFree(p);
   for (auto& e : h->evs) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
@@ -903,6 +1077,7 @@ int smcphys_destroy(smcphys_handle* h) {
 
 int smcphys_set_stream(smcphys_handle* h, void* cuda_stream) {
   if (!h) return fail(SMCPHYS_EINVAL, "NULL handle");
+  if (!h->kids.empty()) return fail(SMCPHYS_ESTATE, "a multi-device handle runs every shard on its own stream");
   CK(cudaSetDevice(h->cfg.device));
   if (h->stream) CK(cudaStreamSynchronize(h->stream));
   if (h->own_stream && h->stream) cudaStreamDestroy(h->stream);
@@ -913,6 +1088,7 @@ int smcphys_set_stream(smcphys_handle* h, void* cuda_stream) {
 
 int smcphys_set_profiling(smcphys_handle* h, int32_t on) {
   if (!h) return fail(SMCPHYS_EINVAL, "NULL handle");
+  if (!h->kids.empty()) h = h->kids[0];
   h->prof = on != 0;
   return 0;
 }
@@ -920,6 +1096,7 @@ int smcphys_set_profiling(smcphys_handle* h, int32_t on) {
 int smcphys_kernel_time(smcphys_handle* h, int32_t kclass, double* ms_total, int64_t* groups) {
   if (!h || !ms_total) return fail(SMCPHYS_EINVAL, "NULL argument");
   if (kclass < 0 || kclass >= SMCPHYS_K_CLASSES) return fail(SMCPHYS_EINVAL, "unknown kernel class");
+  if (!h->kids.empty()) h = h->kids[0];
   CK(cudaSetDevice(h->cfg.device));
   CK(cudaStreamSynchronize(h->stream));
   double tot = 0;
@@ -942,6 +1119,13 @@ int smcphys_kernel_time(smcphys_handle* h, int32_t kclass, double* ms_total, int
 
 int smcphys_synchronize(smcphys_handle* h) {
   if (!h) return fail(SMCPHYS_EINVAL, "NULL handle");
+  if (!h->kids.empty()) {
+    for (auto* k : h->kids) {
+      int rc = smcphys_synchronize(k);
+      if (rc) return rc;
+    }
+    return 0;
+  }
   CK(cudaSetDevice(h->cfg.device));
   CK(cudaStreamSynchronize(h->stream));
   return 0;
@@ -951,7 +1135,17 @@ int smcphys_set_trial(smcphys_handle* h, const double init_pos[3], const double 
                       int32_t T) {
   if (!h || !init_pos || !init_vel || (!obs && T > 0)) return fail(SMCPHYS_EINVAL, "NULL argument");
   if (T < 0 || T > h->cfg.max_timesteps) return fail(SMCPHYS_EINVAL, "T exceeds max_timesteps");
+  if (!h->kids.empty()) {
+    for (auto* k : h->kids) {
+      int rc = smcphys_set_trial(k, init_pos, init_vel, obs, T);
+      if (rc) return rc;
+    }
+    h->T = T;
+    h->trial_set = true;
+    return 0;
+  }
   CK(cudaSetDevice(h->cfg.device));
+  CK(cudaStreamSynchronize(h->stream));  // the previous trial's copy may still read h->obs
   for (int c = 0; c < 3; c++) { h->tp.x0[c] = (float)init_pos[c]; h->tp.v0[c] = (float)init_vel[c]; }
   h->tp.sigma_obs = h->cfg.observation_noise;
   h->tp.sigma_tr = h->cfg.transition_noise;
@@ -960,7 +1154,6 @@ int smcphys_set_trial(smcphys_handle* h, const double init_pos[3], const double 
   h->steps_done = -1;
   h->trial_set = true;
   if (T > 0) {
-    CK(cudaStreamSynchronize(h->stream));  // h->obs is about to be the source of an async copy
     CK(cudaMemcpyAsync(h->d_obs, h->obs.data(), sizeof(double) * 3 * T, cudaMemcpyHostToDevice, h->stream));
   }
   return 0;
@@ -1028,8 +1221,11 @@ int smcphys_pf_resample_local(smcphys_handle* h, int32_t t) {
   philox4x32_10(h->cfg.seed, 0u, (uint32_t)t, 0u, (uint32_t)ST_RESAMPLE, r);
   {
     ProfScope ps(h, SMCPHYS_K_WEIGHTS);
-    LAUNCH(k_cdf, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, &h->ctl->gmax, n, (u64)0, 1);
-    LAUNCH(k_index, nblk(n, 256), 256, h->stream, h->B, h->ctl, n, n, (u64)r[0], &h->ctl->W, (u64)0, (int64_t)0, n, 1);
+    LAUNCH(k_cdf, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, &h->ctl->gmax, n, (u64)0, 1, (const u64*)nullptr);
+    if (h->cfg.resampler == SMCPHYS_RESAMPLE_MULTINOMIAL)
+      LAUNCH(k_index_multi, nblk(n, 256), 256, h->stream, h->B, h->ctl, n, &h->ctl->W, h->cfg.seed, t, (int64_t)0, n, 1);
+    else
+      LAUNCH(k_index, nblk(n, 256), 256, h->stream, h->B, h->ctl, n, n, (u64)r[0], &h->ctl->W, (u64)0, (int64_t)0, n, 1);
   }
   ProfScope ps(h, SMCPHYS_K_GATHER);
   LAUNCH(k_gather, nblk(n, 256), 256, h->stream, h->B, h->ctl, n, n, (int64_t)0, 1);
@@ -1058,10 +1254,150 @@ int smcphys_pf_rejuvenate_from(smcphys_handle* h, int32_t t, int32_t R, int32_t 
   return 0;
 }
 
+// ---------------------------------------------------------------- sharded run (NCCL ranks or a one-process group)
+#define NCCLCK(expr)                                                                                         \
+  do {                                                                                                       \
+    ncclResult_t _r = (expr);                                                                                \
+    if (_r != ncclSuccess) return fail(SMCPHYS_ECUDA, std::string(#expr) + ": " + nccl().GetErrorString(_r)); \
+  } while (0)
+
+// one-process group: every shard's stream waits until all shards have reached this point
+static int group_sync(std::vector<smcphys_handle*>& S) {
+  if (S.size() < 2) return 0;
+  for (auto* s : S) {
+    CK(cudaSetDevice(s->cfg.device));
+    CK(cudaEventRecord(s->ev_sync, s->stream));
+  }
+  for (auto* s : S) {
+    CK(cudaSetDevice(s->cfg.device));
+    for (auto* o : S)
+      if (o != s) CK(cudaStreamWaitEvent(s->stream, o->ev_sync, 0));
+  }
+  return 0;
+}
+
+// One PF step of a sharded filter: S = the shards this process drives (one with an NCCL communicator, or all
+// shards of a one-process group).  Nothing here waits on the host.
+static int sharded_step(std::vector<smcphys_handle*>& S, int t, int R) {
+  const bool use_nccl = S[0]->comm != nullptr;
+  int rc = 0;
+  for (auto* s : S) {
+    rc = smcphys_pf_extend(s, t, nullptr);  // local max -> ctl->gmax
+    if (rc) return rc;
+    if (!use_nccl) LAUNCH(k_copy_lmax, 1, 1, s->stream, s->ctl);
+  }
+  // global max of the log weights
+  if (use_nccl) {
+    for (auto* s : S) NCCLCK(nccl().AllReduce(&s->ctl->gmax, &s->ctl->gmax, 1, ncclDouble, ncclMax, s->comm, s->stream));
+  } else {
+    rc = group_sync(S);
+    if (rc) return rc;
+    for (auto* s : S) {
+      CK(cudaSetDevice(s->cfg.device));
+      LAUNCH(k_local_max, 1, 1, s->stream, s->ctl, s->d_peers, s->nranks);
+    }
+  }
+  // integer weight sums of every shard, visible to every shard
+  for (auto* s : S) {
+    CK(cudaSetDevice(s->cfg.device));
+    const int64_t n = s->cfg.num_particles;
+    ProfScope ps(s, SMCPHYS_K_WEIGHTS);
+    LAUNCH(k_weight_sums, s->ntiles, TILE_THREADS, s->stream, s->B, s->ctl, &s->ctl->gmax, n, s->ntiles, 0,
+           s->cfg.ess_num, s->cfg.ess_den, t, s->d_ess, s->d_lse, s->d_res, s->d_sums3);
+  }
+  if (use_nccl) {
+    for (auto* s : S) NCCLCK(nccl().AllGather(s->d_sums3, s->d_all, 3, ncclUint64, s->comm, s->stream));
+  } else {
+    rc = group_sync(S);
+    if (rc) return rc;
+  }
+  uint32_t r[4];
+  philox4x32_10(S[0]->cfg.seed, 0u, (uint32_t)t, 0u, (uint32_t)ST_RESAMPLE, r);
+  // decision, CDF, ancestors, and the offspring stored into their destination shard
+  for (auto* s : S) {
+    CK(cudaSetDevice(s->cfg.device));
+    const int64_t n = s->cfg.num_particles, N = s->cfg.global_particles;
+    {
+      ProfScope ps(s, SMCPHYS_K_WEIGHTS);
+      LAUNCH(k_decide, 1, 1, s->stream, s->ctl, use_nccl ? (const u64*)s->d_all : (const u64*)nullptr, s->d_peers,
+             s->nranks, s->rank, N, s->cfg.ess_num, s->cfg.ess_den, (u64)r[0], t, s->d_ess, s->d_lse, s->d_res);
+      LAUNCH(k_cdf, s->ntiles, TILE_THREADS, s->stream, s->B, s->ctl, &s->ctl->gmax, n, (u64)0, 1,
+             (const u64*)&s->ctl->W_before);
+      LAUNCH(k_index_sh, nblk(n, 256), 256, s->stream, s->B, s->ctl, n, N);
+    }
+    ProfScope ps(s, SMCPHYS_K_GATHER);
+    LAUNCH(k_push, nblk(n, 256), 256, s->stream, s->B, s->ctl, s->d_peers, n);
+    LAUNCH(k_push_hist, dim3(nblk(n, 256), (unsigned)((t + GH_ROWS) / GH_ROWS)), 256, s->stream, s->B, s->ctl, s->d_peers,
+           n, t + 1);
+  }
+  // every shard's stores have landed before anyone reads its new buffer
+  if (use_nccl) {
+    for (auto* s : S) NCCLCK(nccl().AllReduce(s->d_bar, s->d_bar, 1, ncclInt, ncclSum, s->comm, s->stream));
+  } else {
+    rc = group_sync(S);
+    if (rc) return rc;
+  }
+  for (auto* s : S) {
+    CK(cudaSetDevice(s->cfg.device));
+    const int64_t n = s->cfg.num_particles;
+    {
+      ProfScope ps(s, SMCPHYS_K_GATHER);
+      LAUNCH(k_post_resample, nblk(n, 256), 256, s->stream, s->B, s->ctl, n);
+    }
+    rc = smcphys_pf_rejuvenate(s, t, R, nullptr);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+static int copy_stats(smcphys_handle* h, int32_t R, smcphys_step_stats* per_step) {
+  const int T = h->T;
+  std::vector<double> ess(T), lse(T);
+  std::vector<int> res(T);
+  std::vector<u64> acc(T);
+  CK(cudaSetDevice(h->cfg.device));
+  CK(cudaMemcpyAsync(ess.data(), h->d_ess, sizeof(double) * T, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(lse.data(), h->d_lse, sizeof(double) * T, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(res.data(), h->d_res, sizeof(int) * T, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaMemcpyAsync(acc.data(), h->d_acc, sizeof(u64) * T, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  for (int t = 0; t < T; t++) {
+    per_step[t].ess = ess[t];
+    per_step[t].lse = lse[t];
+    per_step[t].resampled = res[t];
+    per_step[t].pad_ = 0;
+    per_step[t].accept_rate = R > 0 ? (double)acc[t] / ((double)h->cfg.num_particles * R) : 0.0;
+  }
+  return 0;
+}
+
 int smcphys_run_smc(smcphys_handle* h, int32_t R, smcphys_step_stats* per_step) {
+  if (!h) return fail(SMCPHYS_EINVAL, "NULL handle");
+  if (!h->kids.empty() || h->cfg.global_particles != h->cfg.num_particles) {
+    std::vector<smcphys_handle*> S;
+    if (!h->kids.empty()) S = h->kids;
+    else S.push_back(h);
+    for (auto* s : S) {
+      if (!s->trial_set) return fail(SMCPHYS_ESTATE, "no trial: call smcphys_set_trial first");
+      if (!s->comm && s->nranks != (int)S.size())
+        return fail(SMCPHYS_ESTATE, "sharded handle without a communicator: call smcphys_comm_init_rank (one process "
+                                    "per GPU) or use smcphys_create_multi, or drive the smcphys_pf_* phases yourself");
+      if (s->cfg.resampler != SMCPHYS_RESAMPLE_SYSTEMATIC)
+        return fail(SMCPHYS_ESTATE, "the sharded filter resamples systematically (order preserving offspring ranges)");
+    }
+    if (R < 0) R = S[0]->cfg.rejuvenation_moves;
+    int rc = 0;
+    for (auto* s : S) {
+      rc = smcphys_pf_init(s);
+      if (rc) return rc;
+    }
+    const int T = S[0]->T;
+    for (int t = 0; t < T && !rc; t++) rc = sharded_step(S, t, R);
+    if (rc) return rc;
+    if (per_step && T > 0) return copy_stats(S[0], R, per_step);
+    return 0;
+  }
   NEED_TRIAL(h);
-  if (h->cfg.global_particles != h->cfg.num_particles)
-    return fail(SMCPHYS_ESTATE, "run_smc needs an unsharded filter; drive a sharded one through the pf_* phases");
   if (R < 0) R = h->cfg.rejuvenation_moves;
   int rc = smcphys_pf_init(h);
   for (int t = 0; t < h->T && !rc; t++) {
@@ -1070,25 +1406,136 @@ int smcphys_run_smc(smcphys_handle* h, int32_t R, smcphys_step_stats* per_step) 
     rc = rc ? rc : smcphys_pf_rejuvenate(h, t, R, nullptr);
   }
   if (rc) return rc;
-  if (per_step && h->T > 0) {
-    const int T = h->T;
-    std::vector<double> ess(T), lse(T);
-    std::vector<int> res(T);
-    std::vector<u64> acc(T);
-    CK(cudaMemcpyAsync(ess.data(), h->d_ess, sizeof(double) * T, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaMemcpyAsync(lse.data(), h->d_lse, sizeof(double) * T, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaMemcpyAsync(res.data(), h->d_res, sizeof(int) * T, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaMemcpyAsync(acc.data(), h->d_acc, sizeof(u64) * T, cudaMemcpyDeviceToHost, h->stream));
-    CK(cudaStreamSynchronize(h->stream));
-    for (int t = 0; t < T; t++) {
-      per_step[t].ess = ess[t];
-      per_step[t].lse = lse[t];
-      per_step[t].resampled = res[t];
-      per_step[t].pad_ = 0;
-      per_step[t].accept_rate = R > 0 ? (double)acc[t] / ((double)h->cfg.num_particles * R) : 0.0;
+  if (per_step && h->T > 0) return copy_stats(h, R, per_step);
+  return 0;
+}
+
+// ---------------------------------------------------------------- communicator / group set-up
+static void fill_own_peer(smcphys_handle* h, Peer& p) {
+  for (int b = 0; b < 2; b++) { p.xt[b] = h->B.xt[b]; p.st[b] = h->B.st[b]; p.e[b] = h->B.e[b]; p.qs[b] = h->B.qs[b]; }
+  p.cdf = h->B.cdf;
+  p.ctl = h->ctl;
+  p.sums = h->d_sums3;
+}
+
+int smcphys_comm_unique_id(uint8_t id[SMCPHYS_UNIQUE_ID_BYTES]) {
+  if (!id) return fail(SMCPHYS_EINVAL, "NULL id");
+  if (!nccl().load()) return fail(SMCPHYS_ECUDA, nccl().err);
+  static_assert(sizeof(ncclUniqueId) == SMCPHYS_UNIQUE_ID_BYTES, "ncclUniqueId size");
+  ncclUniqueId u;
+  NCCLCK(nccl().GetUniqueId(&u));
+  memcpy(id, &u, sizeof(u));
+  return 0;
+}
+
+int smcphys_comm_init_rank(smcphys_handle* h, const uint8_t id[SMCPHYS_UNIQUE_ID_BYTES], int32_t nranks, int32_t rank) {
+  if (!h || !id) return fail(SMCPHYS_EINVAL, "NULL argument");
+  if (!h->kids.empty() || h->comm) return fail(SMCPHYS_ESTATE, "handle already spans several shards");
+  const int64_t n = h->cfg.num_particles;
+  if (nranks < 2 || nranks > SMCPHYS_MAX_RANKS || rank < 0 || rank >= nranks)
+    return fail(SMCPHYS_EINVAL, "comm_init_rank: need 2 <= nranks <= 64 and 0 <= rank < nranks");
+  if (h->cfg.global_particles != n * nranks || h->cfg.particle_offset != n * rank)
+    return fail(SMCPHYS_EINVAL, "comm_init_rank: the handle must hold the slots [rank n, (rank+1) n) of N = nranks n");
+  if (!nccl().load()) return fail(SMCPHYS_ECUDA, nccl().err);
+  CK(cudaSetDevice(h->cfg.device));
+  ncclUniqueId u;
+  memcpy(&u, id, sizeof(u));
+  NCCLCK(nccl().CommInitRank(&h->comm, nranks, u, rank));
+  h->nranks = nranks;
+  h->rank = rank;
+  // exchange CUDA IPC handles of the buffers the peers store into / read from
+  const int NB = 11;
+  void* mine[NB] = {h->B.xt[0], h->B.xt[1], h->B.st[0], h->B.st[1], h->B.e[0], h->B.e[1], h->B.qs[0], h->B.qs[1],
+                    h->B.cdf, h->ctl, h->d_sums3};
+  std::vector<cudaIpcMemHandle_t> hs(NB), all((size_t)NB * nranks);
+  for (int b = 0; b < NB; b++) CK(cudaIpcGetMemHandle(&hs[b], mine[b]));
+  DevScratch m;
+  char *d_send = nullptr, *d_recv = nullptr;
+  const size_t bytes = sizeof(cudaIpcMemHandle_t) * NB;
+  CK(m.get(&d_send, bytes));
+  CK(m.get(&d_recv, bytes * nranks));
+  CK(cudaMemcpyAsync(d_send, hs.data(), bytes, cudaMemcpyHostToDevice, h->stream));
+  NCCLCK(nccl().AllGather(d_send, d_recv, bytes, ncclChar, h->comm, h->stream));
+  CK(cudaMemcpyAsync(all.data(), d_recv, bytes * nranks, cudaMemcpyDeviceToHost, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  std::vector<Peer> peers(nranks);
+  for (int r = 0; r < nranks; r++) {
+    if (r == rank) { fill_own_peer(h, peers[r]); continue; }
+    void* p[NB];
+    for (int b = 0; b < NB; b++) {
+      cudaError_t e = cudaIpcOpenMemHandle(&p[b], all[(size_t)r * NB + b], cudaIpcMemLazyEnablePeerAccess);
+      if (e != cudaSuccess)
+        return fail(SMCPHYS_ECUDA, std::string("cudaIpcOpenMemHandle (peer buffers of rank ") + std::to_string(r) +
+                                       "): " + cudaGetErrorString(e));
+      h->ipc_opened.push_back(p[b]);
+    }
+    Peer& q = peers[r];
+    q.xt[0] = (float*)p[0]; q.xt[1] = (float*)p[1]; q.st[0] = (float*)p[2]; q.st[1] = (float*)p[3];
+    q.e[0] = (double*)p[4]; q.e[1] = (double*)p[5]; q.qs[0] = (double*)p[6]; q.qs[1] = (double*)p[7];
+    q.cdf = (u64*)p[8]; q.ctl = (Ctl*)p[9]; q.sums = (u64*)p[10];
+  }
+  CK(cudaMemcpyAsync(h->d_peers, peers.data(), sizeof(Peer) * nranks, cudaMemcpyHostToDevice, h->stream));
+  CK(cudaStreamSynchronize(h->stream));
+  return 0;
+}
+
+int smcphys_create_multi(const smcphys_config* cfg, int32_t n_shards, const int32_t* devices, smcphys_handle** out) {
+  if (!cfg || !out || !devices) return fail(SMCPHYS_EINVAL, "NULL argument");
+  if (n_shards < 1 || n_shards > SMCPHYS_MAX_RANKS) return fail(SMCPHYS_EINVAL, "n_shards must be in [1, 64]");
+  if (cfg->struct_size != (int32_t)sizeof(smcphys_config)) return fail(SMCPHYS_EINVAL, "smcphys_config size mismatch");
+  smcphys_handle* g = new smcphys_handle();
+  g->cfg = *cfg;
+  g->cfg.global_particles = cfg->num_particles * n_shards;
+  int rc = 0;
+  for (int r = 0; r < n_shards && !rc; r++) {
+    smcphys_config c = *cfg;
+    c.device = devices[r];
+    c.global_particles = cfg->num_particles * n_shards;
+    c.particle_offset = cfg->num_particles * r;
+    smcphys_handle* k = nullptr;
+    rc = smcphys_create(&c, &k);
+    if (rc) break;
+    k->parent = g; k->nranks = n_shards; k->rank = r;
+    g->kids.push_back(k);
+    if (n_shards > 1 && cudaEventCreateWithFlags(&k->ev_sync, cudaEventDisableTiming) != cudaSuccess)
+      rc = fail(SMCPHYS_ECUDA, "cudaEventCreate failed");
+  }
+  // peer access between the devices of the group, then every shard's table of everyone's buffers
+  for (int a = 0; a < n_shards && !rc && n_shards > 1; a++)
+    for (int b = 0; b < n_shards && !rc; b++) {
+      if (devices[a] == devices[b]) continue;
+      int can = 0;
+      cudaDeviceCanAccessPeer(&can, devices[a], devices[b]);
+      if (!can) { rc = fail(SMCPHYS_ECUDA, "devices of the group cannot access each other's memory (no P2P)"); break; }
+      cudaSetDevice(devices[a]);
+      cudaError_t e = cudaDeviceEnablePeerAccess(devices[b], 0);
+      if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) rc = fail(SMCPHYS_ECUDA, cudaGetErrorString(e));
+      cudaGetLastError();
+    }
+  if (!rc && n_shards > 1) {
+    std::vector<Peer> peers(n_shards);
+    for (int r = 0; r < n_shards; r++) fill_own_peer(g->kids[r], peers[r]);
+    for (auto* k : g->kids) {
+      cudaSetDevice(k->cfg.device);
+      if (cudaMemcpyAsync(k->d_peers, peers.data(), sizeof(Peer) * n_shards, cudaMemcpyHostToDevice, k->stream) != cudaSuccess ||
+          cudaStreamSynchronize(k->stream) != cudaSuccess) {
+        rc = fail(SMCPHYS_ECUDA, "peer table upload failed");
+        break;
+      }
     }
   }
+  if (rc) { smcphys_destroy(g); return rc; }
+  *out = g;
   return 0;
+}
+
+int64_t smcphys_total_particles(smcphys_handle* h) {
+  if (!h) return 0;
+  return h->kids.empty() ? h->cfg.num_particles : h->cfg.num_particles * (int64_t)h->kids.size();
+}
+int32_t smcphys_steps_done(smcphys_handle* h) {
+  if (!h) return -1;
+  return h->kids.empty() ? h->steps_done : h->kids[0]->steps_done;
 }
 
 // current buffer index (synchronises)
@@ -1101,6 +1548,22 @@ static int current_buffer(smcphys_handle* h, int* cur) {
 }
 
 int smcphys_get_particles(smcphys_handle* h, double* e, double* log_w, double* score, float* traj) {
+  if (h && !h->kids.empty()) {
+    // shard r holds the global slots [r n, (r+1) n): scalars concatenate, trajectory rows interleave
+    const int64_t n = h->cfg.num_particles, G = (int64_t)h->kids.size();
+    const int T = h->kids[0]->steps_done;
+    std::vector<float> tmp;
+    if (traj && T > 0) tmp.resize((size_t)3 * T * n);
+    for (int64_t r = 0; r < G; r++) {
+      int rc = smcphys_get_particles(h->kids[r], e ? e + r * n : nullptr, log_w ? log_w + r * n : nullptr,
+                                     score ? score + r * n : nullptr, tmp.empty() ? nullptr : tmp.data());
+      if (rc) return rc;
+      if (!tmp.empty())
+        for (int64_t row = 0; row < (int64_t)3 * T; row++)
+          memcpy(traj + row * (n * G) + r * n, tmp.data() + row * n, sizeof(float) * n);
+    }
+    return 0;
+  }
   NEED_TRIAL(h);
   if (h->steps_done < 0) return fail(SMCPHYS_ESTATE, "get_particles before the filter ran");
   const int64_t n = h->cfg.num_particles;
@@ -1130,6 +1593,7 @@ int smcphys_get_particles(smcphys_handle* h, double* e, double* log_w, double* s
 }
 
 int smcphys_get_states(smcphys_handle* h, float* state13) {
+  if (h && !h->kids.empty()) return fail(SMCPHYS_ESTATE, "get_states: not available on a multi-device handle");
   NEED_TRIAL(h);
   if (h->steps_done < 0) return fail(SMCPHYS_ESTATE, "get_states before the filter ran");
   if (!state13) return fail(SMCPHYS_EINVAL, "NULL output");
@@ -1138,8 +1602,9 @@ int smcphys_get_states(smcphys_handle* h, float* state13) {
   if (rc) return rc;
   // re-simulated with orientation tracking (the rejuvenation kernel does not carry a sphere's quaternion)
   float* soa = h->B.st[cur ^ 1];
+  DevScratch m;
   float* aos = nullptr;
-  CK(cudaMalloc(&aos, sizeof(float) * 13 * n));
+  CK(m.get(&aos, (size_t)13 * n));
   if (h->steps_done == 0) {
     soa = h->B.st[cur];
   } else if (h->cfg.shape == SMCPHYS_SPHERE) {
@@ -1152,40 +1617,75 @@ int smcphys_get_states(smcphys_handle* h, float* state13) {
   LAUNCH(k_soa_to_aos, nblk(n, 256), 256, h->stream, soa, aos, n);
   CK(cudaMemcpyAsync(state13, aos, sizeof(float) * 13 * n, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  cudaFree(aos);
   return 0;
 }
 
+// log marginal likelihood estimate = sum over resampling steps of (LSE - log N) (kept on the device, Ctl::log_ml) plus
+// the same term of the current weights: global max and integer sum W by the kernels of the resampling step (and the
+// collectives of the sharded filter; on NCCL ranks this call is collective).
 int smcphys_get_log_ml(smcphys_handle* h, double* log_ml) {
-  NEED_TRIAL(h);
-  if (h->steps_done < 0 || !log_ml) return fail(SMCPHYS_ESTATE, "get_log_ml before the filter ran");
-  if (h->cfg.global_particles != h->cfg.num_particles)
-    return fail(SMCPHYS_ESTATE, "get_log_ml: a sharded filter keeps its estimate on the host");
-  const int64_t n = h->cfg.num_particles;
-  std::vector<double> lw(n);
-  Ctl c;
-  CK(cudaMemcpyAsync(lw.data(), h->B.logw, sizeof(double) * n, cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaMemcpyAsync(&c, h->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, h->stream));
-  CK(cudaStreamSynchronize(h->stream));
-  double mx = -INFINITY;
-  for (int64_t i = 0; i < n; i++) mx = std::max(mx, lw[i]);
+  if (!h || !log_ml) return fail(SMCPHYS_EINVAL, "NULL argument");
+  std::vector<smcphys_handle*> S;
+  if (!h->kids.empty()) S = h->kids;
+  else S.push_back(h);
+  for (auto* s : S)
+    if (!s->trial_set || s->steps_done < 0) return fail(SMCPHYS_ESTATE, "get_log_ml before the filter ran");
+  const bool use_nccl = S[0]->comm != nullptr;
+  if (!use_nccl && S[0]->cfg.global_particles != S[0]->cfg.num_particles && S.size() == 1)
+    return fail(SMCPHYS_ESTATE, "get_log_ml: a phase-driven sharded filter keeps its estimate on the host");
+  for (auto* s : S) {
+    CK(cudaSetDevice(s->cfg.device));
+    const int64_t n = s->cfg.num_particles;
+    LAUNCH(k_step_begin, 1, 1, s->stream, s->ctl);
+    LAUNCH(k_block_max, nblk(n, 256), 256, s->stream, s->B.logw, n, s->ctl);
+    LAUNCH(k_publish_max, 1, 1, s->stream, s->ctl, (double*)nullptr);
+    if (!use_nccl && S.size() > 1) LAUNCH(k_copy_lmax, 1, 1, s->stream, s->ctl);
+  }
+  if (use_nccl) {
+    for (auto* s : S) NCCLCK(nccl().AllReduce(&s->ctl->gmax, &s->ctl->gmax, 1, ncclDouble, ncclMax, s->comm, s->stream));
+  } else if (S.size() > 1) {
+    int rc = group_sync(S);
+    if (rc) return rc;
+    for (auto* s : S) {
+      CK(cudaSetDevice(s->cfg.device));
+      LAUNCH(k_local_max, 1, 1, s->stream, s->ctl, s->d_peers, s->nranks);
+    }
+  }
   u64 W = 0;
-  for (int64_t i = 0; i < n; i++) W += weight_q(lw[i], mx);
-  *log_ml = c.log_ml + mx + std::log((double)W / 549755813888.0) - std::log((double)n);
+  Ctl c;
+  for (auto* s : S) {
+    CK(cudaSetDevice(s->cfg.device));
+    const int64_t n = s->cfg.num_particles;
+    LAUNCH(k_weight_sums, s->ntiles, TILE_THREADS, s->stream, s->B, s->ctl, &s->ctl->gmax, n, s->ntiles, 0,
+           s->cfg.ess_num, s->cfg.ess_den, 0, (double*)nullptr, (double*)nullptr, (int*)nullptr, s->d_sums3);
+    u64 sums[3 * SMCPHYS_MAX_RANKS];
+    if (use_nccl) {
+      NCCLCK(nccl().AllGather(s->d_sums3, s->d_all, 3, ncclUint64, s->comm, s->stream));
+      CK(cudaMemcpyAsync(sums, s->d_all, sizeof(u64) * 3 * s->nranks, cudaMemcpyDeviceToHost, s->stream));
+    } else {
+      CK(cudaMemcpyAsync(sums, s->d_sums3, sizeof(u64) * 3, cudaMemcpyDeviceToHost, s->stream));
+    }
+    CK(cudaMemcpyAsync(&c, s->ctl, sizeof(Ctl), cudaMemcpyDeviceToHost, s->stream));
+    CK(cudaStreamSynchronize(s->stream));
+    for (int r = 0; r < (use_nccl ? s->nranks : 1); r++) W += sums[3 * r];
+  }
+  *log_ml = c.log_ml + c.gmax + std::log((double)W / 549755813888.0) - std::log((double)S[0]->cfg.global_particles);
   return 0;
 }
 
 int smcphys_predict(smcphys_handle* h, int32_t n_steps, float* pos_out, float* obs_out) {
+  if (h && !h->kids.empty()) return fail(SMCPHYS_ESTATE, "predict: not available on a multi-device handle");
   NEED_TRIAL(h);
   if (h->steps_done < 0) return fail(SMCPHYS_ESTATE, "predict before the filter ran");
   if (n_steps < 1) return fail(SMCPHYS_EINVAL, "n_steps < 1");
   const int64_t n = h->cfg.num_particles;
   int cur = 0, rc = current_buffer(h, &cur);
   if (rc) return rc;
+  DevScratch m;
   float *d_pos = nullptr, *d_obs = nullptr;
   size_t bytes = sizeof(float) * 3 * (size_t)n_steps * n;
-  if (pos_out) CK(cudaMalloc(&d_pos, bytes));
-  if (obs_out) CK(cudaMalloc(&d_obs, bytes));
+  if (pos_out) CK(m.get(&d_pos, (size_t)3 * n_steps * n));
+  if (obs_out) CK(m.get(&d_obs, (size_t)3 * n_steps * n));
   if (h->cfg.shape == SMCPHYS_SPHERE)
     LAUNCH(k_predict<SHAPE_SPHERE>, nblk(n, PF_BLOCK), PF_BLOCK, h->stream, h->B.e[cur], h->B.st[cur], h->tp, h->sp, n,
            h->cfg.particle_offset, h->cfg.seed, h->cfg.substeps, h->steps_done, n_steps, d_pos, d_obs);
@@ -1195,8 +1695,6 @@ int smcphys_predict(smcphys_handle* h, int32_t n_steps, float* pos_out, float* o
   if (pos_out) CK(cudaMemcpyAsync(pos_out, d_pos, bytes, cudaMemcpyDeviceToHost, h->stream));
   if (obs_out) CK(cudaMemcpyAsync(obs_out, d_obs, bytes, cudaMemcpyDeviceToHost, h->stream));
   CK(cudaStreamSynchronize(h->stream));
-  cudaFree(d_pos);
-  cudaFree(d_obs);
   return 0;
 }
 
@@ -1212,15 +1710,6 @@ double smcphys_resample_offset(uint64_t seed, int32_t t) {
   uint32_t r[4];
   philox4x32_10(seed, 0u, (uint32_t)t, 0u, (uint32_t)ST_RESAMPLE, r);
   return (double)r[0] / 4294967296.0;
-}
-// #{k in [0,N) : tau_k < C}; tau is non-decreasing in k
-static int64_t count_below(u64 C, u64 U0, u64 W, int64_t N) {
-  int64_t lo = 0, hi = N;  // first k with tau_k >= C
-  while (lo < hi) {
-    int64_t mid = (lo + hi) >> 1;
-    if (sys_threshold(U0, (u64)mid, W, (u64)N) < C) lo = mid + 1; else hi = mid;
-  }
-  return lo;
 }
 int smcphys_pf_offspring_range(uint64_t W_before, uint64_t W_local, uint64_t W_total, int64_t N, double u0,
                                int64_t* k_lo, int64_t* k_hi) {
@@ -1243,7 +1732,7 @@ int smcphys_pf_pack(smcphys_handle* h, int32_t t, const double* d_global_max, ui
   if (!d_send) return fail(SMCPHYS_EINVAL, "pf_pack: NULL send buffer");
   u64 U0 = (u64)(u0 * 4294967296.0);
   ProfScope ps(h, SMCPHYS_K_GATHER);
-  LAUNCH(k_cdf, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, d_global_max, n, (u64)W_before, 0);
+  LAUNCH(k_cdf, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, d_global_max, n, (u64)W_before, 0, (const u64*)nullptr);
   const int64_t words = 17 + 3 * (int64_t)(t + 1);
   // a shard's offspring can outnumber its particles; the index scratch holds n, so go in slabs of n
   for (int64_t off = 0; off < count; off += n) {
@@ -1267,7 +1756,7 @@ int smcphys_pf_gather_local(smcphys_handle* h, int32_t t, const double* d_global
   if (count == 0) return 0;
   u64 U0 = (u64)(u0 * 4294967296.0);
   ProfScope ps(h, SMCPHYS_K_GATHER);
-  LAUNCH(k_cdf, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, d_global_max, n, (u64)W_before, 0);
+  LAUNCH(k_cdf, h->ntiles, TILE_THREADS, h->stream, h->B, h->ctl, d_global_max, n, (u64)W_before, 0, (const u64*)nullptr);
   LAUNCH(k_index, nblk(count, 256), 256, h->stream, h->B, h->ctl, n, h->cfg.global_particles, U0, (const u64*)nullptr,
          (u64)W_total, k_lo, count, 0);
   LAUNCH(k_gather, nblk(count, 256), 256, h->stream, h->B, h->ctl, n, count, slot0, 0);
@@ -1302,20 +1791,6 @@ int smcphys_pf_unpack(smcphys_handle* h, int32_t t, const float* d_recv, int32_t
 }
 
 // ---------------------------------------------------------------- stateless entries (host pointers)
-}  // extern "C"
-struct DevMem {  // frees on scope exit
-  std::vector<void*> p;
-  ~DevMem() { for (void* q : p) cudaFree(q); }
-  template <class T> cudaError_t get(T** out, size_t count) {
-    void* q = nullptr;
-    cudaError_t e = cudaMalloc(&q, count * sizeof(T) + 16);
-    if (e == cudaSuccess) p.push_back(q);
-    *out = (T*)q;
-    return e;
-  }
-};
-extern "C" {
-
 static int use_device(int32_t device) {
   int ndev = smcphys_device_count();
   if (ndev <= 0) return fail(SMCPHYS_ECUDA, "no CUDA device (libsmcphys has no CPU path)");
@@ -1332,7 +1807,7 @@ int smcphys_sim_step(int32_t device, int32_t shape, int32_t S, double ceiling_ha
   int rc = use_device(device);
   if (rc) return rc;
   if (n == 0) return 0;
-  DevMem m;
+  DevScratch m;
   float *aos, *soa, *r;
   CK(m.get(&aos, (size_t)13 * n)); CK(m.get(&soa, (size_t)13 * n)); CK(m.get(&r, (size_t)n));
   cudaStream_t st = 0;
@@ -1359,7 +1834,7 @@ int smcphys_simulate(int32_t device, int32_t shape, int32_t S, double ceiling_ha
   int rc = use_device(device);
   if (rc) return rc;
   if (n == 0) return 0;
-  DevMem m;
+  DevScratch m;
   cudaStream_t st = 0;
   float *d_e, *d_xt, *d_mu = nullptr, *d_soa, *d_aos;
   double *d_ed, *d_q;
@@ -1397,7 +1872,7 @@ int smcphys_simulate(int32_t device, int32_t shape, int32_t S, double ceiling_ha
 }
 
 // shared by the two weight entries: max -> integer sums (+ tile offsets) on a scratch handle-less Bufs
-static int weights_on_device(const double* log_w, int64_t n, DevMem& m, Bufs& B, Ctl** ctl_out, cudaStream_t st) {
+static int weights_on_device(const double* log_w, int64_t n, DevScratch& m, Bufs& B, Ctl** ctl_out, cudaStream_t st) {
   Ctl* ctl;
   int ntiles = (int)((n + TILE - 1) / TILE);
   memset(&B, 0, sizeof(B));
@@ -1417,7 +1892,7 @@ int smcphys_fp32_peak(int32_t device, double* tflops) {
   if (!tflops) return fail(SMCPHYS_EINVAL, "NULL output");
   int rc = use_device(device);
   if (rc) return rc;
-  DevMem m;
+  DevScratch m;
   float* d;
   CK(m.get(&d, 4));
   cudaDeviceProp prop;
@@ -1445,7 +1920,7 @@ int smcphys_weight_stats(int32_t device, const double* log_w, int64_t n, double*
   if (n < 1 || n > (1ll << 24) || !log_w) return fail(SMCPHYS_EINVAL, "n must be in [1, 2^24] and log_w non-NULL");
   int rc = use_device(device);
   if (rc) return rc;
-  DevMem m;
+  DevScratch m;
   Bufs B;
   Ctl *ctl, c;
   rc = weights_on_device(log_w, n, m, B, &ctl, 0);
@@ -1464,7 +1939,7 @@ int smcphys_resample_systematic(int32_t device, const double* log_w, int64_t n, 
   if (!(u0 >= 0.0 && u0 < 1.0)) return fail(SMCPHYS_EINVAL, "u0 must be in [0, 1)");
   int rc = use_device(device);
   if (rc) return rc;
-  DevMem m;
+  DevScratch m;
   Bufs B;
   Ctl* ctl;
   cudaStream_t st = 0;
@@ -1473,7 +1948,7 @@ int smcphys_resample_systematic(int32_t device, const double* log_w, int64_t n, 
   int64_t* d_out;
   CK(m.get(&d_out, (size_t)n));
   int ntiles = (int)((n + TILE - 1) / TILE);
-  LAUNCH(k_cdf, ntiles, TILE_THREADS, st, B, ctl, &ctl->gmax, n, (u64)0, 0);
+  LAUNCH(k_cdf, ntiles, TILE_THREADS, st, B, ctl, &ctl->gmax, n, (u64)0, 0, (const u64*)nullptr);
   LAUNCH(k_index, nblk(n, 256), 256, st, B, ctl, n, n, (u64)(u0 * 4294967296.0), &ctl->W, (u64)0, (int64_t)0, n, 0);
   LAUNCH(k_idx_to_i64, nblk(n, 256), 256, st, B.idx, d_out, n);
   CK(cudaMemcpyAsync(idx_out, d_out, sizeof(int64_t) * n, cudaMemcpyDeviceToHost, st));

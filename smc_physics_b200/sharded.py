@@ -1,5 +1,13 @@
 """One particle filter sharded over the ranks of a torch.distributed group (one process per GPU).
 
+The product path is INSIDE libsmcphys (include/smcphys.h, smcphys_comm_init_rank + smcphys_run_smc): NCCL all-reduce /
+all-gather for the weight normalisation, the ESS decision and the offspring ranges on the device, offspring stored
+into the destination rank's buffers through peer memory, no host synchronisation per step.  `ShardedFilter` below only
+ships the NCCL unique id over torch.distributed and makes the same set_trial / run_smc / get_particles calls as a
+single-GPU caller.  The phase-by-phase driver that follows (`PhaseShardedFilter`, `LocalShards`) is the same protocol
+spelled out on the host over the smcphys_pf_* phase API; it is what the CPU tests (gloo, world_size 2 and 3) exercise
+with a stand-in shard, and a second, independent implementation the device path is checked against.
+
 Rank r holds the contiguous global particle slots [r*n, (r+1)*n).  Extend / weight / rejuvenate need no
 communication.  Per PF step the ranks exchange (a) one double (MAX all-reduce of the largest log weight), (b) three
 integers per rank (all-gather of the integer weight sums W, S1, S2) from which every rank takes the same ESS
@@ -82,7 +90,48 @@ class _CudaShard:
 
 
 class ShardedFilter:
-    """run_smc (Inference/particle_filter.jl:37-81) over particles_per_rank x world_size particles."""
+    """run_smc (Inference/particle_filter.jl:37-81) over particles_per_rank x world_size particles, one rank per GPU,
+    all of it inside libsmcphys (NCCL + peer memory); torch.distributed only carries the 128-byte NCCL id."""
+
+    def __init__(self, particles_per_rank, shape=api.SPHERE, substeps=5, max_timesteps=120, rejuvenation_moves=1,
+                 device=0, seed=1234, stream=None, group=None, **cfg):
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.n = int(particles_per_rank)
+        self.N = self.n * self.world
+        if self.N > (1 << 24):
+            raise ValueError("global particle count %d exceeds 2^24 (integer weight arithmetic bound)" % self.N)
+        self.R = int(rejuvenation_moves)
+        self.pf = api.ParticleFilter(num_particles=self.n, global_particles=self.N, particle_offset=self.rank * self.n,
+                                     shape=shape, substeps=substeps, max_timesteps=max_timesteps,
+                                     rejuvenation_moves=rejuvenation_moves, device=device, seed=seed, **cfg)
+        if stream is not None:
+            self.pf.set_stream(stream.cuda_stream)
+        if self.world > 1:
+            box = [api.ParticleFilter.comm_unique_id() if self.rank == 0 else None]
+            dist.broadcast_object_list(box, src=0, group=group)
+            self.pf.comm_init(box[0], self.world, self.rank)
+        self.T = 0
+
+    def set_trial(self, init_pos, init_vel, obs):
+        self.T = np.asarray(obs).reshape(-1, 3).shape[0]
+        self.pf.set_trial(init_pos, init_vel, obs)
+
+    def run_smc(self, R=-1, want_stats=True):
+        return self.pf.run_smc(self.R if R < 0 else R, want_stats=want_stats)
+
+    def get_particles(self, **kw):
+        return self.pf.get_particles(**kw)
+
+    def get_log_ml(self):
+        return self.pf.get_log_ml()
+
+    def close(self):
+        self.pf.close()
+
+
+class PhaseShardedFilter:
+    """The same filter driven phase by phase from the host (smcphys_pf_* + torch.distributed collectives)."""
 
     def __init__(self, particles_per_rank, shape=api.SPHERE, substeps=5, max_timesteps=120, rejuvenation_moves=1,
                  device=0, seed=1234, stream=None, group=None, shard=None, **cfg):

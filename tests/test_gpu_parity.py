@@ -7,6 +7,8 @@ Tolerances:
   T3  resampling indices and integer weight sums                   bit exact
   T4  posterior mean / sd of the elasticity vs the oracle         within 3 Monte Carlo standard errors
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -320,3 +322,104 @@ def test_sharded_phases_bit_identical_to_single_shard(sp, shape, G, n):
     assert np.array_equal(one["score"], many["score"])
     assert np.array_equal(one["traj"], many["traj"])
     assert np.allclose([s["ess"] for s in stats], [s["ess"] for s in st2], rtol=1e-12)
+
+
+# ------------------------------------------------------------------ sharded filter inside the library
+@pytest.mark.parametrize("shape,G,n", [(0, 2, 500), (0, 4, 256), (0, 3, 1000), (1, 3, 200)])
+def test_device_sharded_group_bit_identical_to_single_shard(sp, shape, G, n):
+    """smcphys_create_multi: G shards in one handle (here all on device 0), the resampling decision, the offspring
+    ranges and the exchange taken on the device (k_decide / k_index_sh / k_push through the peer table).  Same
+    particles as the unsharded filter with N = G n, bit for bit, and the same log marginal likelihood."""
+    T, R = 25, 2
+    path = _truth_path(shape, 0.6, T)
+    with sp.ParticleFilter(num_particles=G * n, shape=shape, substeps=5, max_timesteps=T, seed=21) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        stats = pf.run_smc(R=R)
+        one = pf.get_particles(want_traj=True)
+        ml1 = pf.get_log_ml()
+    with sp.ParticleFilter(devices=[0] * G, num_particles=n, shape=shape, substeps=5, max_timesteps=T, seed=21) as pf:
+        assert pf.n == G * n
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        st2 = pf.run_smc(R=R)
+        many = pf.get_particles(want_traj=True)
+        ml2 = pf.get_log_ml()
+        # a second run on the same handle starts from scratch
+        pf.run_smc(R=R, want_stats=False)
+        again = pf.get_particles(want_score=False)
+    assert sum(s["resampled"] for s in stats) >= 2
+    assert [s["resampled"] for s in stats] == [s["resampled"] for s in st2]
+    for k in ("e", "log_w", "score", "traj"):
+        assert np.array_equal(one[k], many[k]), k
+    assert np.array_equal(again["e"], one["e"])
+    assert np.allclose([s["ess"] for s in stats], [s["ess"] for s in st2], rtol=1e-12)
+    assert abs(ml1 - ml2) < 1e-9 * (1 + abs(ml1))
+
+
+def test_log_ml_on_device_matches_oracle(sp):
+    T = 12
+    path = _truth_path(0, 0.6, T)
+    with sp.ParticleFilter(num_particles=64, shape=0, substeps=5, max_timesteps=T, seed=99) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        pf.run_smc(R=0)                      # no rejuvenation: identical draws, identical weights
+        ml = pf.get_log_ml()
+    ref = orc.run_smc(0, 64, 0, 5, INIT_POS, INIT_VEL, path, seed=99, f32=True)
+    assert abs(ml - ref["log_ml"]) < 1e-6 * (1 + abs(ref["log_ml"]))
+
+
+def _nccl_worker(rank, world, port, shape, n, T, R, q):
+    import os
+    import sys
+    import torch
+    import torch.distributed as dist
+    sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", rank))
+    try:
+        from smc_physics_b200.sharded import ShardedFilter
+        f = ShardedFilter(particles_per_rank=n, shape=shape, substeps=5, max_timesteps=T, rejuvenation_moves=R,
+                          device=rank, seed=21)
+        f.set_trial(INIT_POS, INIT_VEL, _truth_path(shape, 0.6, T))
+        stats = f.run_smc(R)
+        out = f.get_particles(want_traj=True)
+        ml = f.get_log_ml()
+        q.put((rank, out["e"], out["log_w"], out["score"], out["traj"], [s["resampled"] for s in stats], ml))
+        dist.barrier()
+        f.close()
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("shape,n", [(0, 1000), (1, 300)])
+def test_nccl_ranks_bit_identical_to_single_shard(sp, shape, n):
+    """The path bench.py --gpus N runs: one process per GPU, smcphys_comm_init_rank (NCCL + CUDA IPC), collective
+    smcphys_run_smc.  Needs >= 2 visible devices (skipped on the single-GPU box)."""
+    import torch
+    import torch.multiprocessing as mp
+    world = min(torch.cuda.device_count(), 4)
+    if world < 2:
+        pytest.skip("needs >= 2 CUDA devices")
+    T, R = 25, 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = 29600 + (os.getpid() % 2000)
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, shape, n, T, R, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    outs = sorted([q.get(timeout=300) for _ in procs], key=lambda o: o[0])
+    for p in procs:
+        p.join(timeout=120)
+        assert p.exitcode == 0
+    with sp.ParticleFilter(num_particles=world * n, shape=shape, substeps=5, max_timesteps=T, seed=21) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, _truth_path(shape, 0.6, T))
+        stats = pf.run_smc(R=R)
+        one = pf.get_particles(want_traj=True)
+        ml = pf.get_log_ml()
+    assert sum(s["resampled"] for s in stats) >= 2
+    for o in outs:
+        assert o[5] == [s["resampled"] for s in stats]
+        assert abs(o[6] - ml) < 1e-9 * (1 + abs(ml))
+    assert np.array_equal(np.concatenate([o[1] for o in outs]), one["e"])
+    assert np.array_equal(np.concatenate([o[2] for o in outs]), one["log_w"])
+    assert np.array_equal(np.concatenate([o[3] for o in outs]), one["score"])
+    assert np.array_equal(np.concatenate([o[4] for o in outs], axis=2), one["traj"])

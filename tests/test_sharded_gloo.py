@@ -21,8 +21,8 @@ def _worker(rank, world, port, n, T, seed, q):
     dist.init_process_group("gloo", rank=rank, world_size=world)
     try:
         from _cpu_shard import CpuShard
-        from smc_physics_b200.sharded import ShardedFilter
-        f = ShardedFilter(particles_per_rank=n, seed=seed, shard=CpuShard(n, rank, world))
+        from smc_physics_b200.sharded import PhaseShardedFilter
+        f = PhaseShardedFilter(particles_per_rank=n, seed=seed, shard=CpuShard(n, rank, world))
         f.T = T
         stats = f.run_smc(R=0)
         sh = f.shard
