@@ -206,6 +206,49 @@ def gpu_arm(args):
         dist.all_reduce(t, op=dist.ReduceOp.SUM)
         return float(t.item())
 
+    # ---- correctness guard of the multi-GPU path: a small fixed GLOBAL run (2^16 particles, 25 steps, R = 2) through
+    # the same code path as the timed runs; its particles must be bit-identical for every N (integer weights, global
+    # Philox counters).  For N > 1 rank 0 also runs it unsharded on its own GPU and the bench FAILS on a mismatch.
+    import zlib
+    CHK_N, CHK_T, CHK_R = 1 << 16, 25, 2
+    chk_trial = wl.synthetic_trial(shape_id, T=CHK_T, S=S, device=local)
+
+    def fingerprint(e, lw):
+        return "%08x%08x" % (zlib.crc32(np.ascontiguousarray(e).tobytes()), zlib.crc32(np.ascontiguousarray(lw).tobytes()))
+
+    if world == 1:
+        with sp.ParticleFilter(num_particles=CHK_N, shape=shape_id, substeps=S, max_timesteps=CHK_T, device=local,
+                               seed=1234) as cpf:
+            cpf.set_trial(*chk_trial)
+            cpf.run_smc(CHK_R, want_stats=False)
+            o = cpf.get_particles(want_score=False)
+        check = {"global_particles": CHK_N, "timesteps": CHK_T, "moves": CHK_R, "checksum": fingerprint(o["e"], o["log_w"]),
+                 "matches_unsharded": True}
+    else:
+        from smc_physics_b200.sharded import ShardedFilter
+        cf = ShardedFilter(particles_per_rank=CHK_N // world, shape=shape_id, substeps=S, max_timesteps=CHK_T,
+                           rejuvenation_moves=CHK_R, device=local, seed=1234)
+        cf.set_trial(*chk_trial)
+        cf.run_smc(CHK_R, want_stats=False)
+        o = cf.get_particles(want_score=False)
+        parts = [torch.zeros(2, CHK_N // world, dtype=torch.float64, device=dev) for _ in range(world)]
+        dist.all_gather(parts, torch.from_numpy(np.stack([o["e"], o["log_w"]])).to(dev))
+        cf.close()
+        check = None
+        if rank == 0:
+            allp = torch.cat(parts, dim=1).cpu().numpy()
+            with sp.ParticleFilter(num_particles=CHK_N, shape=shape_id, substeps=S, max_timesteps=CHK_T, device=local,
+                                   seed=1234) as cpf:
+                cpf.set_trial(*chk_trial)
+                cpf.run_smc(CHK_R, want_stats=False)
+                o1 = cpf.get_particles(want_score=False)
+            check = {"global_particles": CHK_N, "timesteps": CHK_T, "moves": CHK_R,
+                     "checksum": fingerprint(allp[0], allp[1]),
+                     "matches_unsharded": fingerprint(allp[0], allp[1]) == fingerprint(o1["e"], o1["log_w"])}
+            if not check["matches_unsharded"]:
+                raise SystemExit("bench.py: the %d-GPU filter is NOT bit-identical to the unsharded one on the check run "
+                                 "(%s vs %s)" % (world, check["checksum"], fingerprint(o1["e"], o1["log_w"])))
+
     # ---- warm-up (also gives the per-step resampling record used for the gather bytes)
     pf.set_trial(*trial)
     stats = None
@@ -305,6 +348,7 @@ def gpu_arm(args):
                                     "note": "group time includes the skipped (non-resampling) launches"}},
         "kernel_steps_per_s": wl.kernel_steps(n_global, T, R) / (ms_per_step * 1e-3),
         "posterior_e_mean": e_mean,
+        "check": check,
     }
     if not args.no_cpu_baseline and world == 1:
         cb = cpu_leg(args, shape_id, trial, 1, 0)
