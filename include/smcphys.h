@@ -175,6 +175,10 @@ int smcphys_simulate(int32_t device, int32_t shape, int32_t S, double ceiling_ha
 /* systematic resampling of n log weights with uniform offset u0 in [0,1): idx_out[k] = ancestor of slot k.
  * Stands in for Gen.maybe_resample! (particle_filter.jl:55); see DESIGN.md for why it is systematic. */
 int smcphys_resample_systematic(int32_t device, const double* log_w, int64_t n, double u0, int64_t* idx_out);
+/* multinomial parents as Gen.maybe_resample! draws them (particle_filter.jl:55; Gen 0.4.7): slot k takes 64 Philox bits
+ * u_k of counter (k, t) and the ancestor min{ i : C_i > floor(u_k W / 2^64) } on the same integer CDF. */
+int smcphys_resample_multinomial(int32_t device, const double* log_w, int64_t n, uint64_t seed, int32_t t,
+                                 int64_t* idx_out);
 /* out3 = {max, ESS, LSE}; sums3 = {W, S1, S2} */
 int smcphys_weight_stats(int32_t device, const double* log_w, int64_t n, double* out3, uint64_t* sums3);
 

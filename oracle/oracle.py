@@ -38,6 +38,10 @@ def lib():
                                       C.c_int, fp, dp, dp, C.c_int]
         L.oracle_run_smc.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
                                      C.c_uint64, C.c_double, C.c_int, dp, dp, dp, C.c_int, dp, dp, dp, fp, dp, dp]
+        L.oracle_run_smc_ex.argtypes = [C.c_int, C.c_int, C.c_int64, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double,
+                                        C.c_uint64, C.c_double, C.c_int, C.c_int, C.c_int, dp, dp, dp, C.c_int, dp, dp, dp,
+                                        fp, dp, dp, dp, C.c_int, fp, fp, C.c_int, dp]
+        L.oracle_resample_multinomial.argtypes = [dp, C.c_int64, C.c_uint64, C.c_int, ip]
         L.oracle_resample_systematic.argtypes = [dp, C.c_int64, C.c_double, ip]
         L.oracle_resample_systematic_f64.argtypes = [dp, C.c_int64, C.c_double, ip]
         L.oracle_weight_stats.argtypes = [dp, C.c_int64, dp, up]
@@ -123,6 +127,38 @@ def run_smc(shape, N, R, S, init_pos, init_vel, obs, seed=1234, sigma_obs=float(
                          _dp(iv), _dp(obs), T, _dp(e), _dp(lw), _dp(lt), _fp(traj) if want_traj else None, _dp(stats),
                          _dp(logml))
     return dict(e=e, log_w=lw, ltrans=lt, stats=stats, log_ml=float(logml[0]), traj=traj)
+
+
+def run_smc_ex(shape, N, R, S, init_pos, init_vel, obs, seed=1234, sigma_obs=float(np.float32(0.05)),
+               sigma_tr=float(np.float32(0.075)), prop_sigma=0.1, ceiling_half=0.01, f32=False, threads=1, resampler=0,
+               no_resample=False, want_traj=False, want_score=False, n_pred=0, mcmc_runs=0):
+    """run_smc plus the optional legs: multinomial resampling, get_score, predict, Gaussian-drift MCMC moves at the last
+    step (with no_resample=True, R=0: Inference/mcmc.jl:53-93)."""
+    obs = np.ascontiguousarray(obs, dtype=np.float64)
+    T = obs.shape[0]
+    e, lw, lt = np.zeros(N), np.zeros(N), np.zeros(N)
+    stats, logml = np.zeros((T, 4)), np.zeros(1)
+    traj = np.zeros((T, 3, N), np.float32) if want_traj else None
+    score = np.zeros(N) if want_score else None
+    ppos = np.zeros((n_pred, 3, N), np.float32) if n_pred else None
+    pobs = np.zeros((n_pred, 3, N), np.float32) if n_pred else None
+    etr = np.zeros((mcmc_runs, N)) if mcmc_runs else None
+    ip = np.ascontiguousarray(init_pos, dtype=np.float64)
+    iv = np.ascontiguousarray(init_vel, dtype=np.float64)
+    lib().oracle_run_smc_ex(int(f32), shape, N, R, S, sigma_obs, sigma_tr, prop_sigma, seed, ceiling_half, threads,
+                            int(resampler), int(no_resample), _dp(ip), _dp(iv), _dp(obs), T, _dp(e), _dp(lw), _dp(lt),
+                            _fp(traj) if want_traj else None, _dp(stats), _dp(logml),
+                            _dp(score) if want_score else None, n_pred, _fp(ppos) if n_pred else None,
+                            _fp(pobs) if n_pred else None, mcmc_runs, _dp(etr) if mcmc_runs else None)
+    return dict(e=e, log_w=lw, ltrans=lt, stats=stats, log_ml=float(logml[0]), traj=traj, score=score, pred_pos=ppos,
+                pred_obs=pobs, e_trace=etr)
+
+
+def resample_multinomial(lw, seed, t):
+    lw = np.ascontiguousarray(lw, dtype=np.float64)
+    idx = np.zeros(lw.shape[0], np.int64)
+    lib().oracle_resample_multinomial(_dp(lw), lw.shape[0], seed, t, idx.ctypes.data_as(C.POINTER(C.c_int64)))
+    return idx
 
 
 def resample_systematic(lw, u0, f64_textbook=False):

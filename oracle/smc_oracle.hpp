@@ -453,7 +453,7 @@ struct Philox {
   }
 };
 // streams (counter word 3)
-enum Stream { ST_PRIOR = 0, ST_TRANSITION = 1, ST_PROPOSAL = 2, ST_RESAMPLE = 3, ST_PREDICT = 4 };
+enum Stream { ST_PRIOR = 0, ST_TRANSITION = 1, ST_PROPOSAL = 2, ST_RESAMPLE = 3, ST_PREDICT = 4, ST_RESAMPLE_MULTI = 5 };
 
 // uniform in (0,1) on a 24-bit grid: (top 24 bits + 0.5) * 2^-24   (exact in float32)
 inline double u01(uint32_t bits) { return ((double)(bits >> 8) + 0.5) * (1.0 / 16777216.0); }
@@ -582,6 +582,25 @@ inline void resample_systematic(const double* lw, int64_t n, double u0, int64_t*
     idx[k] = i;
   }
 }
+// Multinomial resampling - what Gen.maybe_resample! draws in Gen 0.4.7 (rand(Categorical(weights)) per slot, called at
+// Inference/particle_filter.jl:55) - on the same integer CDF: slot k takes 64 Philox bits u_k of counter (k, t) and
+// tau_k = floor(u_k W / 2^64); idx[k] = min{ i : C_i > tau_k }.  The reference is unseeded, so only the distribution
+// (parents i.i.d. with probability q_i / W) can be matched; the integer form makes CPU and GPU agree bit for bit.
+inline void resample_multinomial(const double* lw, int64_t n, uint64_t seed, int t, int64_t* idx, int64_t slot0 = 0) {
+  double mx = -INFINITY;
+  for (int64_t i = 0; i < n; i++) mx = std::max(mx, lw[i]);
+  std::vector<uint64_t> C(n);
+  uint64_t acc = 0;
+  for (int64_t i = 0; i < n; i++) { acc += weight_q(lw[i], mx); C[i] = acc; }
+  for (int64_t k = 0; k < n; k++) {
+    uint32_t r[4];
+    Philox::gen(seed, (uint32_t)(slot0 + k), (uint32_t)t, 0, ST_RESAMPLE_MULTI, r);
+    uint64_t u = ((uint64_t)r[0] << 32) | (uint64_t)r[1];
+    uint64_t tau = (uint64_t)(((unsigned __int128)u * acc) >> 64);
+    int64_t i = std::upper_bound(C.begin(), C.end(), tau) - C.begin();
+    idx[k] = std::min(i, n - 1);
+  }
+}
 // textbook float64 version (cross-check only)
 inline void resample_systematic_f64(const double* lw, int64_t n, double u0, int64_t* idx) {
   double mx = -INFINITY;
@@ -629,6 +648,8 @@ struct SmcConfig {
   uint64_t seed = 1234;
   double ceiling_half = 0.01;
   int threads = 1;           // OpenMP threads over particles (the analogue of the reference's pmap workers)
+  int resampler = 0;         // 0 systematic (north_star), 1 multinomial (Gen.maybe_resample!)
+  int no_resample = 0;       // 1: never resample (the `generate` of Inference/mcmc.jl:56: one trace from the prior)
 };
 struct StepStats { double ess, lse, accept_rate; int resampled; };
 
@@ -707,10 +728,11 @@ inline void run_smc(const SmcConfig& cfg, const double init_pos[3], const double
     // maybe_resample!(ess_threshold = N/2)
     WeightStats ws = weight_stats(P.logw.data(), N);
     StepStats stt{ess_of(ws), lse_of(ws), 0.0, 0};
-    if (ess_below(ws, N, 2)) {
+    if (!cfg.no_resample && ess_below(ws, N, 2)) {
       Philox::gen(cfg.seed, 0, (uint32_t)t, 0, ST_RESAMPLE, r);
       double u0 = (double)r[0] / 4294967296.0;
-      resample_systematic(P.logw.data(), N, u0, idx.data());
+      if (cfg.resampler == 1) resample_multinomial(P.logw.data(), N, cfg.seed, t, idx.data());
+      else resample_systematic(P.logw.data(), N, u0, idx.data());
       log_ml += stt.lse - std::log((double)N);
       std::vector<double> e2(N), lt2(N);
       std::vector<State<T>> st2(N);
@@ -749,6 +771,75 @@ inline void run_smc(const SmcConfig& cfg, const double init_pos[3], const double
     WeightStats ws = weight_stats(P.logw.data(), N);
     *log_ml_out = log_ml + lse_of(ws) - std::log((double)N);
   }
+}
+
+// get_score(trace) (written to the CSV `weight` column, Utilities/fileio.jl:267): the log joint of the trace =
+// sum_{s>=1} log N(xt_s; mu_s, sigma_tr) (mu_1 = the file's initial position) + sum_s log N(y_s; xt_s, sigma_obs);
+// the U(0,1) prior of the elasticity contributes 0.
+template <class T>
+inline double trace_score(const SmcConfig& cfg, const double init_pos[3], const double* obs, int Tn, Particles<T>& P, int64_t i) {
+  double sc = P.ltrans[i];
+  for (int s = 0; s < Tn; s++) {
+    double x[3] = {(double)P.X(s, 0, i), (double)P.X(s, 1, i), (double)P.X(s, 2, i)};
+    if (s == 0) sc += normal3_logpdf(x, init_pos, cfg.sigma_tr);
+    sc += normal3_logpdf(obs + 3 * s, x, cfg.sigma_obs);
+  }
+  return sc;
+}
+
+// predict (Inference/particle_filter.jl:84-102): Gen.update with T -> T + n_steps and no constraints samples the new
+// steps from the model: xt ~ N(mu, sigma_tr), observation ~ N(xt, sigma_obs), then PhySMC.step.  Philox counters
+// (particle, t0 + k, 0 | 1, ST_PREDICT) for the transition / observation noise.  pos/obs_out: [n_steps][3][N].
+template <class T>
+inline void predict(const SmcConfig& cfg, Particles<T>& P, int t0, int n_steps, float* pos_out, float* obs_out) {
+  Scene<T> sc((T)cfg.ceiling_half);
+  const int64_t N = P.N;
+  parallel_for(N, cfg.threads, 16, [&](int64_t i) {
+    State<T> s = P.st[i];
+    for (int k = 0; k < n_steps; k++) {
+      uint32_t r[4], r2[4];
+      Philox::gen(cfg.seed, (uint32_t)i, (uint32_t)(t0 + k), 0, ST_PREDICT, r);
+      Philox::gen(cfg.seed, (uint32_t)i, (uint32_t)(t0 + k), 1, ST_PREDICT, r2);
+      double z[4], zo[4];
+      box_muller(r[0], r[1], z[0], z[1]); box_muller(r[2], r[3], z[2], z[3]);
+      box_muller(r2[0], r2[1], zo[0], zo[1]); box_muller(r2[2], r2[3], zo[2], zo[3]);
+      double mu[3] = {(double)s.x.x, (double)s.x.y, (double)s.x.z};
+      float x[3];
+      for (int c = 0; c < 3; c++) {
+        x[c] = (float)(mu[c] + cfg.sigma_tr * z[c]);
+        if (pos_out) pos_out[((size_t)k * 3 + c) * N + i] = x[c];
+        if (obs_out) obs_out[((size_t)k * 3 + c) * N + i] = (float)((double)x[c] + cfg.sigma_obs * zo[c]);
+      }
+      s.x = {(T)x[0], (T)x[1], (T)x[2]};
+      macro_step(sc, cfg.shape, (T)P.e[i], cfg.S, s);
+    }
+  });
+}
+
+// gaussian_drift_mcmc (Inference/mcmc.jl:53-93) on `chains` independent chains: P holds traces generated from the prior
+// over all Tn steps (run_smc with no_resample = 1, R = 0); then `runs` Metropolis-Hastings moves with the particle
+// filter's proposal at the fixed step Tn, move m drawing Philox counter (chain, Tn - 1, m, ST_PROPOSAL).
+// e_trace[m][chain] = elasticity after move m.
+template <class T>
+inline void mcmc_moves(const SmcConfig& cfg, const double init_pos[3], const double init_vel[3], int Tn, Particles<T>& P,
+                       int move0, int runs, double* e_trace) {
+  Scene<T> sc((T)cfg.ceiling_half);
+  const int64_t N = P.N;
+  parallel_for(N, cfg.threads, 4, [&](int64_t i) {
+    for (int m = 0; m < runs; m++) {
+      uint32_t r[4];
+      Philox::gen(cfg.seed, (uint32_t)i, (uint32_t)(Tn - 1), (uint32_t)(move0 + m), ST_PROPOSAL, r);
+      double e_old = P.e[i];
+      double e_new = truncnorm_sample(u01(r[0]), e_old, cfg.prop_sigma, 0.0, 1.0);
+      double fwd = truncnorm_logpdf(e_new, e_old, cfg.prop_sigma, 0.0, 1.0);
+      double bwd = truncnorm_logpdf(e_old, e_new, cfg.prop_sigma, 0.0, 1.0);
+      State<T> s_new;
+      double lt_new = resimulate(sc, cfg, init_pos, init_vel, e_new, P, i, Tn, s_new);
+      double alpha = (lt_new - P.ltrans[i]) - fwd + bwd;
+      if (std::log(u01(r[1])) < alpha) { P.e[i] = e_new; P.ltrans[i] = lt_new; P.st[i] = s_new; }
+      if (e_trace) e_trace[(size_t)m * N + i] = P.e[i];
+    }
+  });
 }
 
 }  // namespace oracle

@@ -65,12 +65,21 @@ static void simulate(int shape, int S, double ceiling_half, double sigma_tr, con
   });
 }
 
+// extras of one run: score[N]; predict (n_pred steps: pos/obs [n_pred][3][N]); mcmc (runs moves at the last step,
+// e_trace [runs][N]) - all optional
+struct Extras { double* score; int n_pred; float* pred_pos; float* pred_obs; int mcmc_runs; double* e_trace; };
+
 template <class T>
 static void smc(const SmcConfig& cfg, const double* init_pos, const double* init_vel, const double* obs, int Tn,
-                double* e_out, double* logw_out, double* ltrans_out, float* traj_out, double* stats_out, double* log_ml) {
+                double* e_out, double* logw_out, double* ltrans_out, float* traj_out, double* stats_out, double* log_ml,
+                const Extras* ex = nullptr) {
   Particles<T> P;
   std::vector<StepStats> st(Tn);
   run_smc<T>(cfg, init_pos, init_vel, obs, Tn, P, st.data(), log_ml);
+  if (ex && ex->mcmc_runs > 0) mcmc_moves<T>(cfg, init_pos, init_vel, Tn, P, 0, ex->mcmc_runs, ex->e_trace);
+  if (ex && ex->score)
+    for (int64_t i = 0; i < cfg.N; i++) ex->score[i] = trace_score<T>(cfg, init_pos, obs, Tn, P, i);
+  if (ex && ex->n_pred > 0) predict<T>(cfg, P, Tn, ex->n_pred, ex->pred_pos, ex->pred_obs);
   for (int64_t i = 0; i < cfg.N; i++) {
     if (e_out) e_out[i] = P.e[i];
     if (logw_out) logw_out[i] = P.logw[i];
@@ -123,6 +132,22 @@ void oracle_run_smc(int prec32, int shape, int64_t N, int R, int S, double sigma
   if (prec32) smc<float>(cfg, init_pos, init_vel, obs, Tn, e_out, logw_out, ltrans_out, traj_out, stats_out, log_ml);
   else smc<double>(cfg, init_pos, init_vel, obs, Tn, e_out, logw_out, ltrans_out, traj_out, stats_out, log_ml);
 }
+// run_smc with the optional legs: resampler (0 systematic, 1 multinomial), no_resample (mcmc.jl generate), score,
+// predict, MCMC moves at the last step
+void oracle_run_smc_ex(int prec32, int shape, int64_t N, int R, int S, double sigma_obs, double sigma_tr, double prop_sigma,
+                       uint64_t seed, double ceiling_half, int threads, int resampler, int no_resample,
+                       const double* init_pos, const double* init_vel, const double* obs, int Tn, double* e_out,
+                       double* logw_out, double* ltrans_out, float* traj_out, double* stats_out, double* log_ml,
+                       double* score_out, int n_pred, float* pred_pos, float* pred_obs, int mcmc_runs, double* e_trace) {
+  SmcConfig cfg;
+  cfg.shape = shape; cfg.N = N; cfg.R = R; cfg.S = S; cfg.sigma_obs = sigma_obs; cfg.sigma_tr = sigma_tr;
+  cfg.prop_sigma = prop_sigma; cfg.seed = seed; cfg.ceiling_half = ceiling_half; cfg.threads = threads > 0 ? threads : 1;
+  cfg.resampler = resampler; cfg.no_resample = no_resample;
+  Extras ex{score_out, n_pred, pred_pos, pred_obs, mcmc_runs, e_trace};
+  if (prec32) smc<float>(cfg, init_pos, init_vel, obs, Tn, e_out, logw_out, ltrans_out, traj_out, stats_out, log_ml, &ex);
+  else smc<double>(cfg, init_pos, init_vel, obs, Tn, e_out, logw_out, ltrans_out, traj_out, stats_out, log_ml, &ex);
+}
+void oracle_resample_multinomial(const double* lw, int64_t n, uint64_t seed, int t, int64_t* idx) { resample_multinomial(lw, n, seed, t, idx); }
 void oracle_resample_systematic(const double* lw, int64_t n, double u0, int64_t* idx) { resample_systematic(lw, n, u0, idx); }
 void oracle_resample_systematic_f64(const double* lw, int64_t n, double u0, int64_t* idx) { resample_systematic_f64(lw, n, u0, idx); }
 // out: mx, ess, lse ; iout: W, S1, S2, below_half

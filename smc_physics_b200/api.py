@@ -65,6 +65,13 @@ def resample_systematic(log_w, u0, device=0):
     return idx
 
 
+def resample_multinomial(log_w, seed, t, device=0):
+    lw = np.ascontiguousarray(log_w, dtype=np.float64)
+    idx = np.zeros(lw.shape[0], np.int64)
+    check(lib().smcphys_resample_multinomial(device, _dp(lw), lw.shape[0], int(seed), int(t), _ip(idx)))
+    return idx
+
+
 def weight_stats(log_w, device=0):
     lw = np.ascontiguousarray(log_w, dtype=np.float64)
     out = np.zeros(3)

@@ -1956,4 +1956,29 @@ int smcphys_resample_systematic(int32_t device, const double* log_w, int64_t n, 
   return 0;
 }
 
+
+int smcphys_resample_multinomial(int32_t device, const double* log_w, int64_t n, uint64_t seed, int32_t t,
+                                 int64_t* idx_out) {
+  if (n < 0 || n > (1ll << 24)) return fail(SMCPHYS_EINVAL, "n must be in [0, 2^24]");
+  if (n == 0) return 0;
+  if (!log_w || !idx_out) return fail(SMCPHYS_EINVAL, "NULL argument");
+  int rc = use_device(device);
+  if (rc) return rc;
+  DevScratch m;
+  Bufs B;
+  Ctl* ctl;
+  cudaStream_t st = 0;
+  rc = weights_on_device(log_w, n, m, B, &ctl, st);
+  if (rc) return rc;
+  int64_t* d_out;
+  CK(m.get(&d_out, (size_t)n));
+  int ntiles = (int)((n + TILE - 1) / TILE);
+  LAUNCH(k_cdf, ntiles, TILE_THREADS, st, B, ctl, &ctl->gmax, n, (u64)0, 0, (const u64*)nullptr);
+  LAUNCH(k_index_multi, nblk(n, 256), 256, st, B, ctl, n, &ctl->W, (u64)seed, (int)t, (int64_t)0, n, 0);
+  LAUNCH(k_idx_to_i64, nblk(n, 256), 256, st, B.idx, d_out, n);
+  CK(cudaMemcpyAsync(idx_out, d_out, sizeof(int64_t) * n, cudaMemcpyDeviceToHost, st));
+  CK(cudaStreamSynchronize(st));
+  return 0;
+}
+
 }  // extern "C"

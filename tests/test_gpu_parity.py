@@ -423,3 +423,92 @@ def test_nccl_ranks_bit_identical_to_single_shard(sp, shape, n):
     assert np.array_equal(np.concatenate([o[2] for o in outs]), one["log_w"])
     assert np.array_equal(np.concatenate([o[3] for o in outs]), one["score"])
     assert np.array_equal(np.concatenate([o[4] for o in outs], axis=2), one["traj"])
+
+
+# ------------------------------------------------------------------ multinomial resampler (Gen parity), score, predict, MCMC
+@pytest.mark.parametrize("n", [1, 2, 33, 1000, 4097, 100003, 1 << 20])
+def test_multinomial_indices_bit_exact(sp, n):
+    """Gen.maybe_resample! (Inference/particle_filter.jl:55) draws multinomial parents; here: 64 Philox bits per slot
+    against the same integer CDF, bit-exact with the oracle, and distributed like the weights."""
+    rng = np.random.default_rng(n + 5)
+    for spread in (0.1, 3.0, 30.0):
+        lw = rng.normal(0, spread, n) - 77.0
+        got = sp.resample_multinomial(lw, seed=9, t=4)
+        want = orc.resample_multinomial(lw, 9, 4)
+        assert np.array_equal(got, want), (n, spread, np.flatnonzero(got != want)[:5])
+    if n >= 100003:
+        lw = rng.normal(0, 1.0, n)
+        w = np.exp(lw - lw.max())
+        w /= w.sum()
+        counts = np.bincount(sp.resample_multinomial(lw, seed=1, t=0), minlength=n)
+        # offspring counts ~ Binomial(n, w_i): aggregate z-score over 64 blocks of particles
+        blocks = np.array_split(np.arange(n), 64)
+        z = [(counts[b].sum() - n * w[b].sum()) / np.sqrt(n * w[b].sum() * (1 - w[b].sum())) for b in blocks]
+        assert np.abs(z).max() < 5.0 and abs(np.mean(z)) < 0.6
+        assert not np.all(np.diff(sp.resample_multinomial(lw, seed=1, t=0)) >= 0)      # not order preserving
+
+
+def test_run_smc_multinomial_matches_oracle_draw_for_draw(sp):
+    T = 12
+    path = _truth_path(0, 0.6, T)
+    with sp.ParticleFilter(num_particles=64, shape=0, substeps=5, max_timesteps=T, seed=99, resampler=sp.MULTINOMIAL) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        stats = pf.run_smc(R=2)
+        out = pf.get_particles(want_traj=True)
+    ref = orc.run_smc_ex(0, 64, 2, 5, INIT_POS, INIT_VEL, path, seed=99, f32=True, want_traj=True, resampler=1)
+    sys_ref = orc.run_smc(0, 64, 2, 5, INIT_POS, INIT_VEL, path, seed=99, f32=True)
+    assert [s["resampled"] for s in stats] == [bool(r) for r in ref["stats"][:, 3]]
+    assert (np.abs(out["e"] - ref["e"]) < 1e-9).mean() > 0.9
+    assert not np.array_equal(ref["e"], sys_ref["e"])          # it is a different resampler
+    same = np.abs(out["e"] - ref["e"]) < 1e-9
+    assert np.abs(out["traj"][:, :, same] - ref["traj"][:, :, same]).max() < 1e-4
+
+
+def test_score_predict_against_oracle(sp):
+    """get_score (the CSV `weight` column, Utilities/fileio.jl:267) and predict (Inference/particle_filter.jl:84-102)
+    against their oracle legs, same Philox counters: compared on the particles that made identical accept / resample
+    decisions (same elasticity to the last bit).  Small N and a short horizon keep the two lineages slot-aligned: one
+    rounding-level flip of a resampling index shifts the slots after it, and the Philox counters go by slot."""
+    T, N, P = 12, 64, 12
+    path = _truth_path(0, 0.5, T)
+    with sp.ParticleFilter(num_particles=N, shape=0, substeps=5, max_timesteps=T, seed=3) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        pf.run_smc(R=1, want_stats=False)
+        out = pf.get_particles(want_traj=True)
+        pos, obs = pf.predict(P, want_obs=True)
+    ref = orc.run_smc_ex(0, N, 1, 5, INIT_POS, INIT_VEL, path, seed=3, f32=True, want_traj=True, want_score=True, n_pred=P)
+    # (device and host libm differ in the last ulp of the truncated-normal sampler: same = to 1e-12, not to the bit)
+    same = (np.abs(out["e"] - ref["e"]) < 1e-12) & (np.abs(out["traj"].astype(np.float64) - ref["traj"]).max(axis=(0, 1)) < 1e-4)
+    assert same.mean() > 0.8, same.mean()
+    rel = np.abs(out["score"][same] - ref["score"][same]) / (1 + np.abs(ref["score"][same]))
+    assert rel.max() < 1e-6, (rel.max(), np.median(rel))
+    dp = np.abs(pos[:, :, same].astype(np.float64) - ref["pred_pos"][:, :, same]).max(axis=(0, 1))
+    do = np.abs(obs[:, :, same].astype(np.float64) - ref["pred_obs"][:, :, same]).max(axis=(0, 1))
+    assert (dp < 1e-4).mean() > 0.97 and (do < 1e-4).mean() > 0.97, ((dp < 1e-4).mean(), np.sort(dp)[-5:])
+    assert np.median(dp) < 1e-6
+    # the predicted observation scatters around the predicted position with sigma_obs
+    sd = (obs.astype(np.float64) - pos).std()
+    assert abs(sd - 0.05) < 0.005
+
+
+def test_mcmc_chain_matches_oracle_draw_for_draw(sp):
+    """gaussian_drift_mcmc (Inference/mcmc.jl:53-93): 64 chains x 50 moves, every move's elasticity against the oracle
+    chain with the same Philox counters."""
+    T, chains, runs = 30, 64, 50
+    path = _truth_path(0, 0.7, T)
+    trace = np.zeros((runs, chains))
+    with sp.ParticleFilter(num_particles=chains, shape=0, substeps=5, max_timesteps=T, seed=11) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        pf.pf_init()
+        for t in range(T):
+            pf.pf_extend(t)                   # generate(): every step from the prior, no resampling
+        for m in range(runs):
+            pf.pf_rejuvenate(T - 1, 1, move0=m)
+            trace[m] = pf.get_particles(want_score=False)["e"]
+    ref = orc.run_smc_ex(0, chains, 0, 5, INIT_POS, INIT_VEL, path, seed=11, f32=True, no_resample=True, mcmc_runs=runs)
+    assert ref["stats"][:, 3].sum() == 0
+    eq = np.abs(trace - ref["e_trace"]) < 1e-12          # device vs host libm: last-ulp differences in the sampler
+    whole = eq.all(axis=0)
+    assert whole.mean() > 0.9, whole.mean()              # a float32 rounding flip at an MH threshold moves one chain
+    assert eq.mean() > 0.95
+    assert np.unique(trace[:, 0]).size > 3               # the chains do move
