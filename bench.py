@@ -36,6 +36,12 @@ def parse_args():
     ap.add_argument("--timesteps", type=int, default=120)
     ap.add_argument("--moves", type=int, default=5)
     ap.add_argument("--substeps", type=int, default=5)
+    ap.add_argument("--config", type=int, default=-1, choices=[-1, 0, 1, 2, 3, 4],
+                    help="BASELINE.json configs[k]: 0 BulletTest_Sphere N=20 R=2 (27 trials), 1 BulletTest_Cube N=1000 R=5 "
+                         "(27 trials), 2 RealFlow Exp1-4 sphere 100k particles/trial (668 trials, S=9), 3 synthetic sphere "
+                         "2^20 x 120 R=5 (the default), 4 synthetic cube 2^21 per GPU (16M on 8)")
+    ap.add_argument("--trial-particles", type=int, default=0, help="configs 0-2: particles per trial (0 = the config's)")
+    ap.add_argument("--max-trials", type=int, default=0, help="configs 0-2: first K trials only (0 = all)")
     ap.add_argument("--cpu-particles", type=int, default=0, help="particle sample of the CPU legs (0 = auto)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     return ap.parse_args()
@@ -84,12 +90,13 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
-def cpu_leg(args, shape_id, trial, steps, warmup):
-    """The CPU restatement (oracle/) on a bounded particle sample of the same trial, all host threads.
+def cpu_leg(args, shape_id, trial, steps, warmup, threads=0):
+    """The CPU restatement (oracle/) on a bounded particle sample of the same trial, all host threads (threads=1: one
+    thread in the reference's loop order, Inference/particle_filter.jl:48-76).
     The only place outside tests/ and smoke() that executes oracle/ — as the reported baseline, never the product."""
     from oracle import oracle as orc
     orc.build()
-    cores = os.cpu_count() or 1
+    cores = threads or os.cpu_count() or 1
     ip, iv, obs = trial
     T = obs.shape[0]
     n = args.cpu_particles
@@ -99,7 +106,7 @@ def cpu_leg(args, shape_id, trial, steps, warmup):
         t0 = time.perf_counter()
         orc.run_smc(shape_id, n0, args.moves, args.substeps, ip, iv, obs, seed=99, threads=cores)
         dt = max(time.perf_counter() - t0, 1e-3)
-        n = int(max(n0, min(1 << 16, n0 * 8.0 / dt)))
+        n = int(max(n0, min(1 << 16, n0 * (8.0 if not threads else 4.0) / dt)))
         n -= n % cores
     times = []
     for k in range(warmup + steps):
@@ -113,7 +120,7 @@ def cpu_leg(args, shape_id, trial, steps, warmup):
     return {"value": n * T / sec, "unit": UNIT, "cores": cores, "kind": "port",
             "sample": "%d particles x %d timesteps, R=%d, S=%d, same trial; oracle/smc_oracle.hpp float64, %d threads "
                       "over particles; %d timed runs" % (n, T, args.moves, args.substeps, cores, len(timed)),
-            "ms_per_step": sec * 1e3, "steps": len(timed)}
+            "ms_per_step": sec * 1e3, "steps": len(timed), "sample_particles": n}
 
 
 def config_of(args, n_gpus):
@@ -124,7 +131,8 @@ def config_of(args, n_gpus):
             "timesteps": args.timesteps, "rejuvenation_moves": args.moves, "substeps": args.substeps,
             "shape": args.shape, "sharding": "particles over ranks" if n_gpus > 1 else "single shard",
             "l2": "working set (retained-position history, %.2f GB per GPU) exceeds the 126 MB L2" %
-                  (args.particles * args.timesteps * 12 / 1e9)}
+                  (args.particles * args.timesteps * 12 / 1e9),
+            "cpu_sample_particles": getattr(args, "cpu_sample_particles", None)}
 
 
 def reference_arm(args):
@@ -139,6 +147,7 @@ def reference_arm(args):
     truth = orc.macro_rollout(shape_id, 0.6, orc.state13(ip, vel=iv), args.timesteps, S=args.substeps)[:, 0:3]
     obs = np.vstack([ip[None], truth[:-1]])
     cb = cpu_leg(args, shape_id, (ip, iv, obs), args.steps, min(args.warmup, 1))
+    args.cpu_sample_particles = cb["sample_particles"]
     line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus,
             "steps": cb["steps"], "warmup": min(args.warmup, 1), "ms_per_step": cb["ms_per_step"],
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
@@ -353,6 +362,196 @@ def gpu_arm(args):
     if not args.no_cpu_baseline and world == 1:
         cb = cpu_leg(args, shape_id, trial, 1, 0)
         line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        line["config"]["cpu_sample_particles"] = cb["sample_particles"]
+        c1 = cpu_leg(args, shape_id, trial, 1, 0, threads=1)
+        line["cpu_baseline_1thread"] = {k: c1[k] for k in ("value", "unit", "cores", "kind", "sample")}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+# ---------------------------------------------------------------- BASELINE.json configs[0..2]: many independent trials
+def load_trials(args, sp, local):
+    """-> (name, shape_id, S, R, N, [(init_pos, init_vel, obs[T,3])]) of configs 0-2.  configs 0/1: the 27 BulletTest
+    stimuli generated by Tests/generate_trajectories.jl on the CUDA simulator (host.generate_trajectories, seed
+    20240830, S = 5); config 2: the 668 RealFlow trials of Exp1-4 (tests/golden/Data, data only; S = 9)."""
+    import tempfile
+    import numpy as np
+    from smc_physics_b200 import host
+    if args.config in (0, 1):
+        shape_name = "Sphere" if args.config == 0 else "Cube"
+        N, R, S = (20, 2, 5) if args.config == 0 else (1000, 5, 5)
+        old = host.DATA_ROOT
+        host.DATA_ROOT = tempfile.mkdtemp(prefix="smcphys_bench_")
+        try:
+            names = host.generate_trajectories(shape_name, seed=20240830, device=local)
+            d = os.path.join(host.DATA_ROOT, "Data/BulletStimulus/New", shape_name)
+            trials = []
+            for f in names:
+                ip, _, iv, obs, T = host.read_obs_file(os.path.join(d, f), "Bullet")
+                trials.append((np.asarray(ip, float), np.asarray(iv, float), obs))
+        finally:
+            host.DATA_ROOT = old
+        name = "BulletTest_%s, Modelv5 %s, SMC num_particles=%d, rejuvenation_moves=%d, 27 generated trials in flight" % (
+            shape_name, shape_name, N, R)
+        return name, (sp.SPHERE if args.config == 0 else sp.CUBE), S, R, N, trials
+    N, R, S = 100000, 5, 9
+    trials = []
+    for ex in ("Exp1", "Exp2", "Exp3", "Exp4"):
+        d = os.path.join(ROOT, "tests", "golden", "Data", "RealFlowData", ex)
+        for f in sorted(host.filter_unwanted_filenames(os.listdir(d)), key=host.trial_order):
+            ip, _, iv, obs, T = host.read_obs_file(os.path.join(d, f))
+            trials.append((np.asarray(ip, float), np.asarray(iv, float), obs))
+    return "RealFlow Exp1-4 batch, Sphere, 100k particles per trial, all trials concurrent", sp.SPHERE, S, R, N, trials
+
+
+def trials_arm(args):
+    """configs 0-2: a step = every trial of the experiment through run_smc once, all trials of a wave in flight (one
+    handle + stream per trial; the analogue of the reference's pmap over trial files, main.jl:54).  value = sum N T /
+    time.  Over several GPUs the trial list is dealt round robin to the ranks, no communication ("replicas")."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import smc_physics_b200 as sp
+    from smc_physics_b200 import workloads as wl
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit("--gpus %d but WORLD_SIZE=%d" % (args.gpus, world))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    name, shape_id, S, R, N, trials = load_trials(args, sp, local)
+    if args.trial_particles:
+        N = args.trial_particles
+    if args.max_trials:
+        trials = trials[:args.max_trials]
+    mine = trials[rank::world]
+    lib = sp.lib()
+    # waves sized by device memory: two history buffers + state per particle
+    budget, waves, cur, used = 120e9, [], [], 0.0
+    for tr in mine:
+        need = N * (24.0 * max(tr[2].shape[0], 1) + 300.0)
+        if cur and used + need > budget:
+            waves.append(cur); cur, used = [], 0.0
+        cur.append(tr); used += need
+    if cur:
+        waves.append(cur)
+
+    def one_pass(e2e, prof=False):
+        """-> (seconds on the device clock of this rank, posterior means, k_rejuvenate ms)"""
+        t_dev, means, rej_ms = 0.0, [], 0.0
+        for wave in waves:
+            pfs = [sp.ParticleFilter(num_particles=N, shape=shape_id, substeps=S, max_timesteps=max(tr[2].shape[0], 1),
+                                     rejuvenation_moves=R, device=local, seed=1234 + 7919 * k) for k, tr in enumerate(wave)]
+            if not e2e:
+                for pf, tr in zip(pfs, wave):
+                    pf.set_trial(*tr)
+                    pf.set_profiling(prof)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for pf, tr in zip(pfs, wave):
+                if e2e:
+                    pf.set_trial(*tr)
+                pf.run_smc(R, want_stats=False)
+            if e2e:
+                for pf in pfs:
+                    means.append(float(pf.get_particles(want_score=False)["e"].mean()))
+            else:
+                for pf in pfs:
+                    pf.synchronize()
+            t_dev += time.perf_counter() - t0
+            for pf in pfs:
+                if prof:
+                    rej_ms += pf.kernel_time(sp.K_REJUVENATE)[0]
+                pf.close()
+        return t_dev, means, rej_ms
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce(x, op):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=op)
+        return float(t.item())
+
+    for _ in range(max(args.warmup, 1)):
+        one_pass(False)
+    clocks = ClockSampler(local)
+    barrier()
+    if rank == 0:
+        clocks.start()
+    l0 = lib.smcphys_launch_count()
+    t_res = 0.0
+    for _ in range(args.steps):
+        t_res += one_pass(False)[0]
+    barrier()
+    launches = lib.smcphys_launch_count() - l0
+    clk = clocks.stop() if rank == 0 else None
+    t_res = reduce(t_res / args.steps, dist.ReduceOp.MAX if world > 1 else None)
+    rej_ms = one_pass(False, prof=True)[2]
+    barrier()
+    t_e2e, means = 0.0, []
+    for _ in range(args.steps):
+        dt, means, _ = one_pass(True)
+        t_e2e += dt
+    barrier()
+    t_e2e = reduce(t_e2e / args.steps, dist.ReduceOp.MAX if world > 1 else None)
+    units = float(N * sum(tr[2].shape[0] for tr in trials))
+    kst = float(sum(wl.kernel_steps(N, tr[2].shape[0], R) for tr in trials))
+    flop = float(sum(sum(wl.flop_rejuvenate(shape_id, S, N, R, t) for t in range(tr[2].shape[0])) for tr in mine))
+    h2d = sum(tr[2].size * 8 + 48 for tr in trials)
+    d2h = len(trials) * N * 16
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    peak_tf = sp.fp32_peak(local)
+    ach = flop / t_res / 1e12
+    line = {"metric": METRIC, "value": units / t_res, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 1), "ms_per_step": t_res * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic" if args.config < 2 else "reference stimuli (RealFlow Exp1-4)",
+            "config": {"workload": name + " (BASELINE.json configs[%d])" % args.config, "trials": len(trials),
+                       "particles_per_trial": N, "frames_total": int(sum(tr[2].shape[0] for tr in trials)),
+                       "rejuvenation_moves": R, "substeps": S, "shape": "sphere" if shape_id == sp.SPHERE else "cube",
+                       "sharding": "trials dealt to ranks, no communication (replicas)" if world > 1 else "single GPU",
+                       "waves": len(waves), "l2": "every run re-creates its filters; histories %s the 126 MB L2" % (
+                           "exceed" if N * 24 * 60 * len(waves[0]) > 126e6 else "fit in")},
+            "clocks": clk,
+            "e2e": {"value": units / t_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "ms_per_step": t_e2e * 1e3},
+            "gpu_launches": int(launches),
+            "roofline": {"kernel": "k_rejuvenate", "bound": "fp32", "achieved": ach, "peak": peak_tf, "unit": "TFLOP/s",
+                         "frac": ach / peak_tf if peak_tf else None, "traffic": None,
+                         "note": "trials overlap on the device, so per-kernel times are not additive: achieved = algorithmic "
+                                 "FLOP of every k_rejuvenate launch / device time of the whole step (a lower bound); the sum "
+                                 "of the per-launch event times is rejuvenate_event_ms",
+                         "rejuvenate_event_ms": rej_ms,
+                         "peak_source": "FP32 FMA probe run in this process (smcphys_fp32_peak)"},
+            "kernel_steps_per_s": kst / t_res, "posterior_e_mean": float(np.mean(means)) if means else None}
+    if not args.no_cpu_baseline and world == 1:
+        # bounded sample: the first trials of the list with the config's particle count (capped), both thread modes
+        from oracle import oracle as orc
+        orc.build()
+        cores = os.cpu_count() or 1
+        ncpu = min(N, 2000)
+        for key, th in (("cpu_baseline", cores), ("cpu_baseline_1thread", 1)):
+            t0, done, k = time.perf_counter(), 0.0, 0
+            while k < len(trials) and time.perf_counter() - t0 < (12.0 if th > 1 else 8.0):
+                ip, iv, obs = trials[k]
+                orc.run_smc(shape_id, ncpu, R, S, ip, iv, obs, seed=1234 + k, threads=th)
+                done += ncpu * obs.shape[0]
+                k += 1
+            sec = time.perf_counter() - t0
+            line[key] = {"value": done / sec, "unit": UNIT, "cores": th, "kind": "port",
+                         "sample": "first %d trials at %d particles each, R=%d, S=%d; oracle/smc_oracle.hpp float64, %d "
+                                   "thread(s) over particles" % (k, ncpu, R, S, th)}
+        line["config"]["cpu_sample_particles"] = ncpu
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -360,7 +559,13 @@ def gpu_arm(args):
 
 if __name__ == "__main__":
     a = parse_args()
+    if a.config == 3:
+        a.shape, a.particles, a.timesteps, a.moves, a.substeps = "sphere", 1 << 20, 120, 5, 5
+    if a.config == 4:
+        a.shape, a.particles, a.timesteps, a.moves, a.substeps = "cube", 1 << 21, 120, 5, 5
     if a.impl == "reference":
         reference_arm(a)
+    elif a.config in (0, 1, 2):
+        trials_arm(a)
     else:
         gpu_arm(a)
