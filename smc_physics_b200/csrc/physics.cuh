@@ -397,6 +397,98 @@ __device__ __noinline__ VelPair solve_plane_contacts(const Contact* c, int nc, f
   return o;
 }
 
+// The same solve with the rows of NC contacts in REGISTERS (every loop over the contacts unrolled): r, the three
+// effective masses den and the right-hand sides / applied impulses, 12 floats per contact; 1 / den is re-taken by the
+// approximate reciprocal where the rolled form reads its stored copy (same instruction, same bits).  The rolled form
+// keeps its rows in local memory, and with 1.6 KB of stack per thread those loads miss L1: `long_scoreboard` was the
+// top stall of the cube kernel and this loop half of its instructions (profiles/r02_cube_*).  Results are bit
+// identical to solve_plane_contacts.
+template <int NC>
+__device__ __forceinline__ VelPair solve_plane_reg(const Contact* c, float restitution, f3 v, f3 w) {
+  const float inv_m = PH_INV_M, inv_i = PH_INV_I_CUBE;
+  const float crest = restitution * PH_STATIC_REST;
+  f3 r[NC];
+  float den[NC][3], rhs[NC][3], app[NC][3];
+#pragma unroll
+  for (int i = 0; i < NC; i++) {
+    r[i] = c[i].r;
+    const float rx2 = r[i].x * r[i].x, ry2 = r[i].y * r[i].y, rz2 = r[i].z * r[i].z;
+    den[i][0] = inv_m + (ry2 + rx2) * inv_i;
+    den[i][1] = inv_m + (rz2 + rx2) * inv_i;
+    den[i][2] = inv_m + (rz2 + ry2) * inv_i;
+    const float relv0 = v.z + (r[i].y * w.x - r[i].x * w.y);
+    const float relv1 = -v.y + (r[i].z * w.x - r[i].x * w.z);
+    const float relv2 = v.x + (r[i].z * w.y - r[i].y * w.z);
+    float rest = 0.f;
+    if (fabsf(relv0) >= PH_REST_THRESH) rest = fmaxf(0.f, -crest * relv0);
+    const float distance = c[i].dist + PH_SLOP;
+    float verr = rest - relv0, perr = 0.f;
+    if (distance > 0.f) verr -= distance / PH_DT;
+    else perr = -distance * PH_ERP / PH_DT;
+#pragma unroll
+    for (int k = 0; k < 3; k++) app[i][k] = 0.f;
+    rhs[i][0] = (perr + verr) * (1.0f / den[i][0]);
+    rhs[i][1] = -relv1 * (1.0f / den[i][1]);
+    rhs[i][2] = -relv2 * (1.0f / den[i][2]);
+  }
+  f3 dv = mk3(0.f, 0.f, 0.f), dw = mk3(0.f, 0.f, 0.f);
+#pragma unroll 1
+  for (int it = 0; it < PH_ITERS; it++) {
+    float resid = 0.f;
+#pragma unroll
+    for (int i = 0; i < NC; i++) {
+      float dimp = rhs[i][0] - (dv.z + (r[i].y * dw.x - r[i].x * dw.y)) * (1.0f / den[i][0]);
+      const float sum = app[i][0] + dimp;
+      if (sum < 0.f) { dimp = -app[i][0]; app[i][0] = 0.f; }
+      else app[i][0] = sum;
+      dv.z += dimp * inv_m;
+      const float q = dimp * inv_i;
+      dw.x += r[i].y * q;
+      dw.y -= r[i].x * q;
+      const float dvel = dimp * den[i][0];
+      resid = fmaxf(resid, dvel * dvel);
+    }
+#pragma unroll
+    for (int i = 0; i < NC; i++) {
+      const float lim = PH_FRICTION * app[i][0];
+      float s1 = app[i][1] + (rhs[i][1] - (-dv.y + (r[i].z * dw.x - r[i].x * dw.z)) * (1.0f / den[i][1]));
+      float s2 = app[i][2] + (rhs[i][2] - (dv.x + (r[i].z * dw.y - r[i].y * dw.z)) * (1.0f / den[i][2]));
+      const float l2 = s1 * s1 + s2 * s2;
+      if (l2 > lim * lim) {
+        const float scl = lim / sqrtf(l2);
+        s1 *= scl;
+        s2 *= scl;
+      }
+      const float d1 = s1 - app[i][1], d2 = s2 - app[i][2];
+      app[i][1] = s1;
+      app[i][2] = s2;
+      dv.y -= d1 * inv_m;
+      dv.x += d2 * inv_m;
+      const float q1 = d1 * inv_i, q2 = d2 * inv_i;
+      dw.x += r[i].z * q1;
+      dw.y += r[i].z * q2;
+      dw.z -= r[i].x * q1 + r[i].y * q2;
+      const float e1 = d1 * den[i][1], e2 = d2 * den[i][2];
+      resid = fmaxf(resid, fmaxf(e1 * e1, e2 * e2));
+    }
+    if (resid <= PH_RESID) break;
+  }
+  VelPair o;
+  o.v = v + dv;
+  o.w = w + dw;
+  return o;
+}
+#ifndef PH_PLANE_ROLLED
+__device__ __noinline__ VelPair solve_plane_contacts_reg(const Contact* c, int nc, float restitution, f3 v, f3 w) {
+  switch (nc) {
+    case 1: return solve_plane_reg<1>(c, restitution, v, w);
+    case 2: return solve_plane_reg<2>(c, restitution, v, w);
+    case 3: return solve_plane_reg<3>(c, restitution, v, w);
+    default: return solve_plane_reg<4>(c, restitution, v, w);
+  }
+}
+#endif
+
 // general contact set of the cube (walls, ceiling, more than the plane manifold), out of line
 __device__ __noinline__ VelPair solve_contacts_cube_call(const Contact* c, int nc, float restitution, f3 v, f3 w) {
   solve_contacts<SHAPE_CUBE>(c, nc, restitution, v, w);
@@ -919,8 +1011,13 @@ __device__ __forceinline__ void substep(const ScenePar& sp, float restitution, B
     const int npl = pm.n;  // the plane-manifold points come first in c[]
     apply_forces(s);
     if (nc > 0) {
+#ifdef PH_PLANE_ROLLED
       const VelPair r = (nc == npl) ? solve_plane_contacts(c, nc, restitution, s.v, s.w)
                                     : solve_contacts_cube_call(c, nc, restitution, s.v, s.w);
+#else
+      const VelPair r = (nc == npl) ? solve_plane_contacts_reg(c, nc, restitution, s.v, s.w)
+                                    : solve_contacts_cube_call(c, nc, restitution, s.v, s.w);
+#endif
       s.v = r.v;
       s.w = r.w;
     }
