@@ -965,12 +965,51 @@ __device__ __noinline__ SphereChain sphere_contacts_near_box(SphereChain s) {
   return s;
 }
 
+// One face contact of the sphere in the contact's own frame: (n, a, b) a cyclic permutation of (x, y, z), normal
+// s e_n with s = +-1, arm r = -h s e_n.  sphere_solve_one on scalars: u_t = (v_a - h s w_b, v_b + h s w_a),
+// r x J = (0, h s J_b, -h s J_a).  Floor: (n, a, b) = (z, x, y), s = +1; x walls: (x, y, z); y walls: (y, z, x).
+__device__ __forceinline__ float face_rhs(float s, float dist, float crest, float vn) {
+  const float vnn = s * vn;
+  float rest = 0.f;
+  if (fabsf(vnn) >= PH_REST_THRESH) rest = fmaxf(0.f, -crest * vnn);
+  const float distance = dist + PH_SLOP;
+  float verr = rest - vnn, perr = 0.f;
+  if (distance > 0.f) verr -= distance / PH_DT;
+  else perr = -distance * PH_ERP / PH_DT;
+  return perr + verr;
+}
+__device__ __forceinline__ void face_solve(float s, float rhs_n, float& vn, float& va, float& vb, float& wa, float& wb) {
+  const float dinv_t = 1.0f / (PH_INV_M + PH_H * PH_H * PH_INV_I_SPHERE);  // 1 / 3.5
+  const float ln = fmaxf(0.f, rhs_n);
+  const float lim = PH_FRICTION * ln;
+  const float hs = PH_H * s;
+  float ja = (va - hs * wb) * (-dinv_t), jb = (vb + hs * wa) * (-dinv_t);
+  const float m2 = ja * ja + jb * jb;
+  if (m2 > lim * lim) {
+    const float scl = lim / sqrtf(m2);
+    ja *= scl;
+    jb *= scl;
+  }
+  vn += s * ln;
+  va += ja;
+  vb += jb;
+  const float k = (PH_H * PH_INV_I_SPHERE) * s;
+  wa += k * jb;
+  wb -= k * ja;
+}
+
 // One 1/240 s substep of the sphere on the chain state (orientation not tracked: it never feeds back into the motion).
-// Floor-only contact and free flight are in line; a body within reach of a box takes the call, with the whole chain
-// state passed through it.
+// In line, on scalars: free flight, the floor, the face of ONE wall (its face region: the centre between the wall's
+// edges, outside its core), and floor + wall face when the solver would not iterate (sphere_contacts_inline's
+// screening: neither normal row pushes / one pushes and the other stays idle).  These are 80 % of the substeps spent
+// within reach of a box in a filter run and all of those away from the boxes; the rest - wall edges, a centre inside
+// a wall, two walls, the ceiling, pairs that iterate - takes the call, with the whole chain state passed through it.
 __device__ __forceinline__ void sphere_chain_substep(SphereChain& c) {
   const float reach = PH_H + PH_THR;
-  const bool near_box = fmaxf(fabsf(c.x.x), fabsf(c.x.y)) > 0.5f - reach || c.x.z > 1.01f - c.ceil_half - reach;
+  const float crest = c.restitution * PH_STATIC_REST;
+  const float ax = fabsf(c.x.x), ay = fabsf(c.x.y);
+  const bool nearx = ax > 0.5f - reach, neary = ay > 0.5f - reach;
+  const bool nearc = c.x.z > 1.01f - c.ceil_half - reach;
   const float d = c.x.z - PH_H;
   {
     const float dt = PH_DT;
@@ -981,8 +1020,53 @@ __device__ __forceinline__ void sphere_chain_substep(SphereChain& c) {
     const float fw = PH_DAMP * (1.0f + wn);
     c.w = mk3(c.w.x + dt * (-fw * c.w.x), c.w.y + dt * (-fw * c.w.y), c.w.z + dt * (-fw * c.w.z));
   }
-  if (near_box) c = sphere_contacts_near_box(c);
-  else if (d < PH_THR) sphere_solve_floor(d, c.restitution, c.v, c.w);
+  if (!(nearx || neary || nearc)) {
+    if (d < PH_THR) face_solve(1.0f, face_rhs(1.0f, d, crest, c.v.z), c.v.z, c.v.x, c.v.y, c.w.x, c.w.y);
+  } else {
+    bool slow = true;
+    const float aw = nearx ? ax : ay;  // distance of the centre from the arena centre across the wall
+    // face region of exactly one wall: closest point of the wall's core box (half thickness 0.01 - margin, spanning
+    // z in [0.011, 1.009]) lies on its inner face and the centre is outside the core
+    if (nearx != neary && !nearc && c.x.z >= 0.011f && aw < 0.501f) {
+      const float cb = aw - 0.51f;                                // sphere_vs_box on the mirrored coordinate
+      const float dl = -(cb + (0.01f - PH_BOX_MARGIN));
+      const float dist = dl - PH_H - PH_BOX_MARGIN;
+      const float sw = (nearx ? c.x.x : c.x.y) >= 0.f ? -1.0f : 1.0f;  // normal: from the wall into the arena
+      // the wall's frame (n, a, b): x wall (x, y, z), y wall (y, z, x)
+      float vn = nearx ? c.v.x : c.v.y, va = nearx ? c.v.y : c.v.z, vb = nearx ? c.v.z : c.v.x;
+      float wa = nearx ? c.w.y : c.w.z, wb = nearx ? c.w.z : c.w.x;
+      const bool hit_w = dist < PH_THR, hit_f = d < PH_THR;
+      slow = false;
+      if (hit_w && hit_f) {
+        const float r0 = face_rhs(1.0f, d, crest, c.v.z), r1 = face_rhs(sw, dist, crest, vn);
+        if (r0 > 0.f && r1 > 0.f) slow = true;
+        else if (r0 > 0.f) {
+          // floor active, wall idle: the wall's normal row must stay idle under the floor's full velocity change
+          const f3 v0 = c.v, w0 = c.w;
+          face_solve(1.0f, r0, c.v.z, c.v.x, c.v.y, c.w.x, c.w.y);
+          const float dvn = (nearx ? c.v.x - v0.x : c.v.y - v0.y) * sw;
+          if (r1 - dvn > 0.f) { c.v = v0; c.w = w0; slow = true; }
+        } else if (r1 > 0.f) {
+          const float vz0 = c.v.z;
+          face_solve(sw, r1, vn, va, vb, wa, wb);
+          // in the wall's frame the floor normal is b (x wall) or a (y wall)
+          const float vz1 = nearx ? vb : va;
+          if (r0 - (vz1 - vz0) > 0.f) slow = true;
+          else {
+            if (nearx) { c.v = mk3(vn, va, vb); c.w = mk3(c.w.x, wa, wb); }
+            else { c.v = mk3(vb, vn, va); c.w = mk3(wb, c.w.y, wa); }
+          }
+        }
+      } else if (hit_w) {
+        face_solve(sw, face_rhs(sw, dist, crest, vn), vn, va, vb, wa, wb);
+        if (nearx) { c.v = mk3(vn, va, vb); c.w = mk3(c.w.x, wa, wb); }
+        else { c.v = mk3(vb, vn, va); c.w = mk3(wb, c.w.y, wa); }
+      } else if (hit_f) {
+        face_solve(1.0f, face_rhs(1.0f, d, crest, c.v.z), c.v.z, c.v.x, c.v.y, c.w.x, c.w.y);
+      }
+    }
+    if (slow) c = sphere_contacts_near_box(c);
+  }
   c.x = c.x + c.v * PH_DT;
 }
 

@@ -438,6 +438,53 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
   return qs;
 }
 
+// The sphere chain on one struct of loop state (physics.cuh, SphereChain): rows walked by one pointer, the row of the
+// next step loaded while the current macro step runs (the loop itself needs ~30 registers, so holding the row costs
+// nothing; an L1 prefetch instead left the load of the row as the top stall of the loop).  TRAJ: also write the
+// simulator output after every step (the CSV trajectory).  Orientation is not integrated (see physics.cuh).
+template <bool TRAJ>
+__device__ __forceinline__ SphereChain sphere_chain_run(float ceil_half, f3 x0, f3 v0, int S, float e,
+                                                        const float* __restrict__ xt, int64_t n, int64_t i, int steps,
+                                                        float* traj) {
+  SphereChain c;
+  c.v = v0; c.w = mk3(0.f, 0.f, 0.f);
+  c.restitution = e; c.ceil_half = ceil_half;
+  c.pk = xt + i; c.n = n; c.qs = 0.0; c.S = S;
+  c.x = x0;
+  c.nx = x0;
+  float* o = TRAJ ? traj + i : nullptr;
+  if (steps > 0) {
+    c.x = mk3(c.pk[0], c.pk[c.n], c.pk[2 * c.n]);
+#pragma unroll 1
+    for (c.k = steps; ; ) {
+      c.pk += 3 * c.n;
+#ifdef RS_L1_PREFETCH
+      if (c.k > 1) {
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(c.pk));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(c.pk + c.n));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(c.pk + 2 * c.n));
+      }
+#else
+      if (c.k > 1) c.nx = mk3(c.pk[0], c.pk[c.n], c.pk[2 * c.n]);
+#endif
+#pragma unroll 1
+      for (c.sub = c.S; c.sub > 0; c.sub--) sphere_chain_substep(c);
+      if (TRAJ) {
+        o[0] = c.x.x; o[c.n] = c.x.y; o[2 * c.n] = c.x.z;
+        o += 3 * c.n;
+      }
+      if (--c.k == 0) break;
+#ifdef RS_L1_PREFETCH
+      c.nx = mk3(c.pk[0], c.pk[c.n], c.pk[2 * c.n]);
+#endif
+      const float dx = c.nx.x - c.x.x, dy = c.nx.y - c.x.y, dz = c.nx.z - c.x.z;
+      c.qs += (double)dx * (double)dx + (double)dy * (double)dy + (double)dz * (double)dz;
+      c.x = c.nx;
+    }
+  }
+  return c;
+}
+
 // The sphere chain of the rejuvenation kernel as a call: inside, the register allocation sees nothing but the
 // chain (body, elasticity, the prefetched row), while the Metropolis-Hastings state of the caller (five doubles,
 // counters, pointers) is parked by the calling convention once per chain instead of being spilled in the substep loop.
@@ -451,40 +498,7 @@ __device__ __noinline__ ChainOut resimulate_call(float ceil_half, f3 x0, f3 v0, 
                                                  const float* __restrict__ xt, int64_t n, int64_t i, int steps) {
   ChainOut o;
   if (SHAPE == SHAPE_SPHERE) {
-    // the sphere chain on one struct of loop state (physics.cuh, SphereChain): rows walked by one pointer, the row of
-    // the next step loaded while the current macro step runs (the loop itself needs ~30 registers, so holding the row
-    // costs nothing; an L1 prefetch instead left the load of the row as the top stall of the loop)
-    SphereChain c;
-    c.v = v0; c.w = mk3(0.f, 0.f, 0.f);
-    c.restitution = e; c.ceil_half = ceil_half;
-    c.pk = xt + i; c.n = n; c.qs = 0.0; c.S = S;
-    c.x = x0;
-    c.nx = x0;
-    if (steps > 0) {
-      c.x = mk3(c.pk[0], c.pk[c.n], c.pk[2 * c.n]);
-#pragma unroll 1
-      for (c.k = steps; ; ) {
-        c.pk += 3 * c.n;
-#ifdef RS_L1_PREFETCH
-        if (c.k > 1) {
-          asm volatile("prefetch.global.L1 [%0];" ::"l"(c.pk));
-          asm volatile("prefetch.global.L1 [%0];" ::"l"(c.pk + c.n));
-          asm volatile("prefetch.global.L1 [%0];" ::"l"(c.pk + 2 * c.n));
-        }
-#else
-        if (c.k > 1) c.nx = mk3(c.pk[0], c.pk[c.n], c.pk[2 * c.n]);
-#endif
-#pragma unroll 1
-        for (c.sub = c.S; c.sub > 0; c.sub--) sphere_chain_substep(c);
-        if (--c.k == 0) break;
-#ifdef RS_L1_PREFETCH
-        c.nx = mk3(c.pk[0], c.pk[c.n], c.pk[2 * c.n]);
-#endif
-        const float dx = c.nx.x - c.x.x, dy = c.nx.y - c.x.y, dz = c.nx.z - c.x.z;
-        c.qs += (double)dx * (double)dx + (double)dy * (double)dy + (double)dz * (double)dz;
-        c.x = c.nx;
-      }
-    }
+    SphereChain c = sphere_chain_run<false>(ceil_half, x0, v0, S, e, xt, n, i, steps, nullptr);
     o.qs = c.qs;
     o.x = c.x; o.v = c.v; o.w = c.w;
     o.q.x = o.q.y = o.q.z = 0.f; o.q.w = 1.f;
@@ -580,6 +594,15 @@ __global__ void __launch_bounds__(RJ_BLOCK)
   if (i0 >= n) return;
   Body s;
   double qs;
+  if (SHAPE == SHAPE_SPHERE && !state_out) {
+    // the trajectory and the transition density of a sphere come from the SAME chain code the rejuvenation kernel
+    // runs (so the trajectory parity tests pin that code); only the state getter needs the orientation
+    const f3 x0 = mk3(tp.x0[0], tp.x0[1], tp.x0[2]), v0 = mk3(tp.v0[0], tp.v0[1], tp.v0[2]);
+    const SphereChain c = mu_out ? sphere_chain_run<true>(sp.ceil_half, x0, v0, S, (float)e[i0], xt, n, i0, T, mu_out)
+                                 : sphere_chain_run<false>(sp.ceil_half, x0, v0, S, (float)e[i0], xt, n, i0, T, nullptr);
+    if (q_out) q_out[i0] = c.qs;
+    return;
+  }
   if (mu_out) qs = resimulate<SHAPE, true, true>(sp, tp, S, (float)e[i0], xt, n, i0, T, s, mu_out);
   else qs = resimulate<SHAPE, true, false>(sp, tp, S, (float)e[i0], xt, n, i0, T, s, nullptr);
   if (q_out) q_out[i0] = qs;
@@ -1849,9 +1872,13 @@ int smcphys_simulate(int32_t device, int32_t shape, int32_t S, double ceiling_ha
   CK(cudaMemcpyAsync(d_e, e, sizeof(float) * n, cudaMemcpyHostToDevice, st));
   if (T > 0) CK(cudaMemcpyAsync(d_xt, xt, sizeof(float) * 3 * (size_t)T * n, cudaMemcpyHostToDevice, st));
   LAUNCH(k_f2d, nblk(n, 256), 256, st, d_e, d_ed, n);
-  if (shape == SMCPHYS_SPHERE)
-    LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, st, d_ed, d_xt, tp, sp, n, S, T, d_mu, d_q, d_soa);
-  else
+  if (shape == SMCPHYS_SPHERE) {
+    // trajectory + transition density through the rejuvenation kernel's chain code, the final state (with the
+    // orientation the chain does not carry) through the general substep: the parity tests see both
+    LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, st, d_ed, d_xt, tp, sp, n, S, T, d_mu, d_q, (float*)nullptr);
+    LAUNCH(k_traj<SHAPE_SPHERE>, nblk(n, RJ_BLOCK), RJ_BLOCK, st, d_ed, d_xt, tp, sp, n, S, T, (float*)nullptr,
+           (double*)nullptr, d_soa);
+  } else
     LAUNCH(k_traj<SHAPE_CUBE>, nblk(n, RJ_BLOCK), RJ_BLOCK, st, d_ed, d_xt, tp, sp, n, S, T, d_mu, d_q, d_soa);
   if (mu_out && T > 0) CK(cudaMemcpyAsync(mu_out, d_mu, sizeof(float) * 3 * (size_t)T * n, cudaMemcpyDeviceToHost, st));
   std::vector<double> q;
