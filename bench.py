@@ -123,6 +123,15 @@ def cpu_leg(args, shape_id, trial, steps, warmup, threads=0):
             "ms_per_step": sec * 1e3, "steps": len(timed), "sample_particles": n}
 
 
+def kernel_source_hash():
+    """sha256 (first 16 hex) of the kernel sources: stamps ncu-derived numbers so that a stale capture is not reported."""
+    import hashlib
+    h = hashlib.sha256()
+    for f in ("physics.cuh", "rng.cuh", "smcphys.cu"):
+        h.update(open(os.path.join(ROOT, "smc_physics_b200", "csrc", f), "rb").read())
+    return h.hexdigest()[:16]
+
+
 def config_of(args, n_gpus):
     return {"workload": "synthetic %s bounce, %d particles/GPU x %d timesteps, rejuvenation_moves=%d, substeps=%d "
                         "(BASELINE.json configs[%d])" % (args.shape, args.particles, args.timesteps, args.moves,
@@ -323,13 +332,19 @@ def gpu_arm(args):
     except OSError:
         pass
     hbm_peak = float(peaks.get("hbm_gbs", 6650.0))
-    # measured DRAM traffic of the mean k_rejuvenate launch, from the committed ncu capture of this same workload
-    traffic = None
+    # measured DRAM traffic of one k_rejuvenate launch (t = 60), from the committed ncu capture of this same workload.
+    # The entry is stamped with a hash of the kernel sources it was captured from: a stale capture gives null.
+    traffic, traffic_note = None, "no ncu capture of this workload under profiles/traffic.json"
     try:
-        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_rejuvenate"]
+        tr = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_rejuvenate_" + args.shape]
         c = tr["config"]
-        if (c["shape"], c["particles"], c["timesteps"], c["moves"], c["substeps"]) == (args.shape, n, T, R, S):
-            traffic = tr["dram_bytes"]
+        if (c["particles"], c["timesteps"], c["moves"], c["substeps"]) == (n, T, R, S):
+            if tr.get("src_sha") == kernel_source_hash():
+                traffic = tr["dram_bytes"]
+                traffic_note = ("dram__bytes_read+write of the t=%d launch (ncu --set full, %s); algorithmic bytes of that "
+                                "launch = R*12*(t+1)*n = %.3g" % (tr["launch_t"], tr["source"], R * 12 * (tr["launch_t"] + 1) * n))
+            else:
+                traffic_note = "profiles/traffic.json was captured from other kernel sources (%s): not reported" % tr.get("src_sha")
     except (OSError, ValueError, KeyError):
         pass
     res_steps = [t for t, s in enumerate(stats or []) if s["resampled"]]
@@ -346,8 +361,7 @@ def gpu_arm(args):
         "gpu_launches": int(launches),
         "roofline": {"kernel": "k_rejuvenate", "bound": "fp32", "achieved": rej_tf, "peak": peak_tf, "unit": "TFLOP/s",
                      "frac": rej_tf / peak_tf if peak_tf else None, "traffic": traffic,
-                     "traffic_note": "dram__bytes_read+write of the t=60 launch (ncu --set full, profiles/); algorithmic "
-                                     "bytes of that launch = R*12*(t+1)*n = %.3g" % (R * 12 * 61 * n),
+                     "traffic_note": traffic_note,
                      "peak_source": "FP32 FMA probe run in this process (smcphys_fp32_peak); not in MEASURED_PEAKS.json",
                      "launches": int(rej_groups), "avg_launch_ms": rej_ms / max(rej_groups, 1),
                      "flop_per_launch_avg": flop_run / T, "share_of_step": shares,

@@ -39,8 +39,13 @@ mutable struct Config
     ess_num::Int64
     ess_den::Int64
     seed::UInt64
+    resampler::Int32          # SYSTEMATIC | MULTINOMIAL (what Gen.maybe_resample! draws, particle_filter.jl:55)
+    pad_::Int32
     Config() = new()
 end
+
+const SYSTEMATIC = Int32(0)
+const MULTINOMIAL = Int32(1)
 
 struct StepStats
     ess::Float64
@@ -128,7 +133,8 @@ Same positional signature as Inference/particle_filter.jl:37.  `gm_args = (sim::
 """
 function run_smc(fname::String, model, gm_args::Tuple, obs, rejuvenation_moves=1, num_particles::Int=20,
                  save_particles=false, output_path=nothing, w2=nothing; seed::Integer=1234,
-                 observation_noise=Float64(0.05f0), transition_noise=Float64(0.075f0))
+                 observation_noise=Float64(0.05f0), transition_noise=Float64(0.075f0),
+                 resampler::Integer=SYSTEMATIC, devices::Union{Nothing,Vector{<:Integer}}=nothing)
     sim, init_state, T = gm_args
     tokens = split(basename(fname), "_")
     csv = split(tokens[3], ".")
@@ -137,9 +143,20 @@ function run_smc(fname::String, model, gm_args::Tuple, obs, rejuvenation_moves=1
     c.num_particles = num_particles; c.global_particles = num_particles; c.particle_offset = 0
     c.max_timesteps = max(T, 1); c.rejuvenation_moves = rejuvenation_moves
     c.observation_noise = observation_noise; c.transition_noise = transition_noise
-    c.ceiling_half = sim.ceiling_half; c.seed = seed
+    c.ceiling_half = sim.ceiling_half; c.seed = seed; c.resampler = resampler
     h = Ref{Ptr{Cvoid}}(C_NULL)
-    check(ccall((:smcphys_create, LIB[]), Cint, (Ref{Config}, Ref{Ptr{Cvoid}}), c, h))
+    if devices === nothing
+        check(ccall((:smcphys_create, LIB[]), Cint, (Ref{Config}, Ref{Ptr{Cvoid}}), c, h))
+    else
+        # ONE filter over several GPUs of this process (smcphys_create_multi): num_particles is split evenly over the
+        # listed devices; everything below (set_trial, run_smc, get_particles) is unchanged - still one ccall each.
+        # save_particles needs the phase entries and stays single-device.
+        num_particles % length(devices) == 0 || error("num_particles must be a multiple of the device count")
+        save_particles && error("save_particles: per-step dumps are single-device")
+        c.num_particles = num_particles ÷ length(devices)
+        check(ccall((:smcphys_create_multi, LIB[]), Cint, (Ref{Config}, Int32, Ptr{Int32}, Ref{Ptr{Cvoid}}),
+                    c, length(devices), Int32.(devices), h))
+    end
     obsm = obs isa AbstractMatrix ? Matrix{Float64}(obs') : reduce(hcat, [Float64.(o) for o in obs])  # 3 × T
     check(ccall((:smcphys_set_trial, LIB[]), Cint, (Ptr{Cvoid}, Ptr{Float64}, Ptr{Float64}, Ptr{Float64}, Int32),
                 h[], Float64.(collect(init_state.position)), Float64.(collect(init_state.linear_vel)), obsm, T))
@@ -189,6 +206,18 @@ function write_to_csv(p::Particles, fname; frames::Int=p.T)
         end
     end
 end
+
+# ---------------------------------------------------------------- one filter over the GPUs of several processes
+# (Julia Distributed workers, one per GPU - the reference's addprocs layout, main.jl:5-9): every worker creates its
+# shard (Config with num_particles = N / nranks, global_particles = N, particle_offset = rank * num_particles), rank 0
+# makes the id and ships it (e.g. remotecall_fetch), every worker calls comm_init_rank; smcphys_run_smc is collective.
+function comm_unique_id()
+    id = Vector{UInt8}(undef, 128)
+    check(ccall((:smcphys_comm_unique_id, LIB[]), Cint, (Ptr{UInt8},), id))
+    id
+end
+comm_init_rank(h::Ptr{Cvoid}, id::Vector{UInt8}, nranks::Integer, rank::Integer) =
+    check(ccall((:smcphys_comm_init_rank, LIB[]), Cint, (Ptr{Cvoid}, Ptr{UInt8}, Int32, Int32), h, id, nranks, rank))
 
 "Parity entry: systematic resampling indices (1-based) for log weights `lw` and uniform offset `u0`."
 function resample_systematic(lw::Vector{Float64}, u0::Float64; device::Integer=0)

@@ -550,16 +550,15 @@ __global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : RJ
     for (int j = 0; j < R; j++) {
       uint32_t r[4];
       philox4x32_10(seed, (uint32_t)(goff + i), (uint32_t)t, (uint32_t)(move0 + j), (uint32_t)ST_PROPOSAL, r);
-      const double e_new = truncnorm_sample(u01(r[0]), e_old, prop_sigma, 0.0, 1.0);
-      const double fwd = truncnorm_logpdf(e_new, e_old, prop_sigma, 0.0, 1.0);
-      const double bwd = truncnorm_logpdf(e_old, e_new, prop_sigma, 0.0, 1.0);
+      double log_qratio;  // log q(e | e') - log q(e' | e)
+      const double e_new = truncnorm_propose(u01(r[0]), e_old, prop_sigma, 0.0, 1.0, &log_qratio);
       const double log_u = log(u01(r[1]));
       const ChainOut o = resimulate_call<SHAPE>(sp.ceil_half, mk3(tp.x0[0], tp.x0[1], tp.x0[2]),
                                                 mk3(tp.v0[0], tp.v0[1], tp.v0[2]), S, (float)e_new, xt_cur, n, i, t + 1);
       const double q_new = o.qs;
       Body s;
       s.x = o.x; s.v = o.v; s.w = o.w; s.q = o.q;
-      const double alpha = -(q_new - q_old) * inv2s2 - fwd + bwd;
+      const double alpha = -(q_new - q_old) * inv2s2 + log_qratio;
       if (log_u < alpha) {
         // accepted: the simulator state goes out right away, so nothing but (e, q) stays live across the moves
         e_old = e_new;

@@ -10,6 +10,7 @@ import pytest
 import __graft_entry__ as entry
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+_ECUDA = -2
 
 
 @pytest.fixture(scope="module")
@@ -106,3 +107,36 @@ def test_bad_arguments_are_reported_not_thrown(L):
     assert L.smcphys_create(C.byref(cfg), C.byref(h)) == -1
     assert L.smcphys_destroy(None) == 0
     assert L.smcphys_set_trial(None, None, None, None, 0) == -1
+
+
+def test_multi_gpu_entries_fail_cleanly_without_a_device(L):
+    """The in-library sharded filter (smcphys_comm_* / smcphys_create_multi): argument checks and no CPU path."""
+    from smc_physics_b200 import _lib
+    cfg = _lib.Config()
+    L.smcphys_config_default(C.byref(cfg))
+    h = _lib._H()
+    devs = (C.c_int32 * 2)(0, 0)
+    rc = L.smcphys_create_multi(C.byref(cfg), 2, devs, C.byref(h))
+    assert rc in (_ECUDA, 0)
+    if rc == 0:
+        L.smcphys_destroy(h)
+    assert L.smcphys_create_multi(C.byref(cfg), 0, devs, C.byref(h)) == -1            # n_shards out of range
+    assert L.smcphys_create_multi(C.byref(cfg), 65, devs, C.byref(h)) == -1
+    assert L.smcphys_comm_init_rank(None, b"\0" * 128, 2, 0) == -1                       # NULL handle
+    assert L.smcphys_comm_unique_id(None) == -1
+    cfg.resampler = 7
+    assert L.smcphys_create(C.byref(cfg), C.byref(h)) == -1                              # unknown resampler
+    assert L.smcphys_total_particles(None) == 0 and L.smcphys_steps_done(None) == -1
+
+
+def test_nccl_is_bound_at_run_time(L):
+    """libsmcphys.so must load without NCCL on the link line (dlopen at first use)."""
+    import subprocess
+    so = os.path.join(ROOT, "smc_physics_b200", "libsmcphys.so")
+    needed = subprocess.run(["readelf", "-d", so], capture_output=True, text=True).stdout
+    assert "libnccl" not in needed
+    buf = C.create_string_buffer(128)
+    rc = L.smcphys_comm_unique_id(buf)
+    assert rc in (0, _ECUDA)          # 0 where a libnccl.so.2 is installed; a clean error where it is not
+    if rc == 0:
+        assert any(b != 0 for b in buf.raw)
