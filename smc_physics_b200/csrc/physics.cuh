@@ -46,7 +46,9 @@ struct Body {
 #define PH_SLOP 1e-5f                     // linearSlop
 #define PH_REST_THRESH 0.2f               // restitutionVelocityThreshold
 #define PH_RESID 1e-7f                    // leastSquaresResidualThreshold
+#ifndef PH_ITERS
 #define PH_ITERS 50                       // numIterations
+#endif
 #define PH_STALL 1e-6f                     // early exit of an infeasible solve: velocity change per sweep
 #define PH_BOX_MARGIN 0.001f              // collision margin of a 0.01-thin btBoxShape
 #define PH_ANG_THRESH 0.78539816339744830962f
@@ -946,6 +948,7 @@ __device__ __forceinline__ void sphere_solve_floor(float d, float restitution, f
 struct SphereChain {
   f3 x, v, w;
   float restitution, ceil_half;
+  float zc;         // centre height above which the ceiling is within reach
   f3 nx;            // the next retained position, loaded one macro step ahead
   const float* pk;  // row pointer of the caller's loop
   long long n;      // row stride
@@ -1009,16 +1012,16 @@ __device__ __forceinline__ void sphere_chain_substep(SphereChain& c) {
   const float crest = c.restitution * PH_STATIC_REST;
   const float ax = fabsf(c.x.x), ay = fabsf(c.x.y);
   const bool nearx = ax > 0.5f - reach, neary = ay > 0.5f - reach;
-  const bool nearc = c.x.z > 1.01f - c.ceil_half - reach;
+  const bool nearc = c.x.z > c.zc;  // zc = 1.01 - ceil_half - reach, kept in the chain state
   const float d = c.x.z - PH_H;
   {
-    const float dt = PH_DT;
-    const float vn = sqrtf(dot3(c.v, c.v));
-    const float f = PH_DAMP * (1.0f + vn);
-    c.v = mk3(c.v.x + dt * (-f * c.v.x), c.v.y + dt * (-f * c.v.y), c.v.z + dt * (PH_G - f * c.v.z));
-    const float wn = sqrtf(dot3(c.w, c.w));
-    const float fw = PH_DAMP * (1.0f + wn);
-    c.w = mk3(c.w.x + dt * (-fw * c.w.x), c.w.y + dt * (-fw * c.w.y), c.w.z + dt * (-fw * c.w.z));
+    // v += dt (g - k v (1 + |v|))  written as  v <- v (1 - dt k (1 + |v|)) + dt g: one multiplier per vector instead of
+    // a product and an FMA per component (7 instructions less per substep); the same number up to the last bit
+    const float a = 1.0f - PH_DT * PH_DAMP, b = -(PH_DT * PH_DAMP);
+    const float gv = fmaf(sqrtf(dot3(c.v, c.v)), b, a);
+    c.v = mk3(c.v.x * gv, c.v.y * gv, fmaf(c.v.z, gv, PH_DT * PH_G));
+    const float gw = fmaf(sqrtf(dot3(c.w, c.w)), b, a);
+    c.w = mk3(c.w.x * gw, c.w.y * gw, c.w.z * gw);
   }
   if (!(nearx || neary || nearc)) {
     if (d < PH_THR) face_solve(1.0f, face_rhs(1.0f, d, crest, c.v.z), c.v.z, c.v.x, c.v.y, c.w.x, c.w.y);
@@ -1091,7 +1094,7 @@ __device__ __forceinline__ void substep(const ScenePar& sp, float restitution, B
     if (near_box) {
       SphereChain a;
       a.x = s.x; a.v = s.v; a.w = s.w; a.restitution = restitution; a.ceil_half = sp.ceil_half;
-      a.pk = nullptr; a.n = 0; a.qs = 0.0; a.k = a.sub = a.S = 0;
+      a.zc = 0.f; a.pk = nullptr; a.n = 0; a.qs = 0.0; a.k = a.sub = a.S = 0;
       a = sphere_contacts_near_box(a);
       s.v = a.v;
       s.w = a.w;

@@ -442,6 +442,10 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
 // next step loaded while the current macro step runs (the loop itself needs ~30 registers, so holding the row costs
 // nothing; an L1 prefetch instead left the load of the row as the top stall of the loop).  TRAJ: also write the
 // simulator output after every step (the CSV trajectory).  Orientation is not integrated (see physics.cuh).
+#ifdef RS_STEP_CLOCK
+// diagnostic build only (tools/bench_kernel.py): SM cycles the warps of a launch spend in each macro step of the chain
+__device__ unsigned long long g_step_clk[4096];
+#endif
 template <bool TRAJ>
 __device__ __forceinline__ SphereChain sphere_chain_run(float ceil_half, f3 x0, f3 v0, int S, float e,
                                                         const float* __restrict__ xt, int64_t n, int64_t i, int steps,
@@ -449,6 +453,7 @@ __device__ __forceinline__ SphereChain sphere_chain_run(float ceil_half, f3 x0, 
   SphereChain c;
   c.v = v0; c.w = mk3(0.f, 0.f, 0.f);
   c.restitution = e; c.ceil_half = ceil_half;
+  c.zc = 1.01f - ceil_half - (PH_H + PH_THR);
   c.pk = xt + i; c.n = n; c.qs = 0.0; c.S = S;
   c.x = x0;
   c.nx = x0;
@@ -467,8 +472,15 @@ __device__ __forceinline__ SphereChain sphere_chain_run(float ceil_half, f3 x0, 
 #else
       if (c.k > 1) c.nx = mk3(c.pk[0], c.pk[c.n], c.pk[2 * c.n]);
 #endif
+#ifdef RS_STEP_CLOCK
+      const long long clk0 = clock64();
+#endif
 #pragma unroll 1
       for (c.sub = c.S; c.sub > 0; c.sub--) sphere_chain_substep(c);
+#ifdef RS_STEP_CLOCK
+      __syncwarp();
+      if ((threadIdx.x & 31) == 0) atomicAdd(&g_step_clk[(steps - c.k) & 4095], (unsigned long long)(clock64() - clk0));
+#endif
       if (TRAJ) {
         o[0] = c.x.x; o[c.n] = c.x.y; o[2 * c.n] = c.x.z;
         o += 3 * c.n;
@@ -1550,6 +1562,18 @@ int smcphys_create_multi(const smcphys_config* cfg, int32_t n_shards, const int3
   *out = g;
   return 0;
 }
+
+#ifdef RS_STEP_CLOCK
+// diagnostic build only: read and clear the per-macro-step cycle counters of the sphere chain
+int smcphys_debug_step_clocks(unsigned long long* out, int32_t n) {
+  if (!out || n < 1 || n > 4096) return fail(SMCPHYS_EINVAL, "bad arguments");
+  CK(cudaDeviceSynchronize());
+  CK(cudaMemcpyFromSymbol(out, g_step_clk, sizeof(unsigned long long) * n));
+  std::vector<unsigned long long> z(4096, 0);
+  CK(cudaMemcpyToSymbol(g_step_clk, z.data(), sizeof(unsigned long long) * 4096));
+  return 0;
+}
+#endif
 
 int64_t smcphys_total_particles(smcphys_handle* h) {
   if (!h) return 0;
