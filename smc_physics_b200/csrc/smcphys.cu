@@ -403,6 +403,10 @@ __global__ void __launch_bounds__(256) k_gather_hist(Bufs B, const Ctl* ctl, int
 // the body is teleported to x~_s, keeps the velocity / orientation the simulator produced, and is stepped.
 // Returns sum_{s>=2} |x~_s - mu'_s|^2.  The next row of x~ is fetched before the current macro step so the
 // load latency hides behind the arithmetic.
+#ifdef RS_STEP_CLOCK
+// diagnostic build only (tools/bench_kernel.py): SM cycles the warps of a launch spend in each macro step of the chain
+__device__ unsigned long long g_step_clk[4096];
+#endif
 template <int SHAPE, bool TRACK_Q, bool TRAJ>
 __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar& tp, int S, float e,
                                              const float* __restrict__ xt, int64_t n, int64_t i, int steps, Body& s,
@@ -429,7 +433,14 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
       qs += (double)dx * (double)dx + (double)dy * (double)dy + (double)dz * (double)dz;
     }
     s.x = mk3(x, y, z);
+#ifdef RS_STEP_CLOCK
+    const long long clk0 = clock64();
+#endif
     macro_step<SHAPE, TRACK_Q>(sp, e, S, s);
+#ifdef RS_STEP_CLOCK
+    __syncwarp();
+    if ((threadIdx.x & 31) == 0) atomicAdd(&g_step_clk[(steps - k) & 4095], (unsigned long long)(clock64() - clk0));
+#endif
     if (TRAJ) {
       o[0] = s.x.x; o[n] = s.x.y; o[2 * n] = s.x.z;
       o += row;
@@ -442,10 +453,6 @@ __device__ __forceinline__ double resimulate(const ScenePar& sp, const TrialPar&
 // next step loaded while the current macro step runs (the loop itself needs ~30 registers, so holding the row costs
 // nothing; an L1 prefetch instead left the load of the row as the top stall of the loop).  TRAJ: also write the
 // simulator output after every step (the CSV trajectory).  Orientation is not integrated (see physics.cuh).
-#ifdef RS_STEP_CLOCK
-// diagnostic build only (tools/bench_kernel.py): SM cycles the warps of a launch spend in each macro step of the chain
-__device__ unsigned long long g_step_clk[4096];
-#endif
 template <bool TRAJ>
 __device__ __forceinline__ SphereChain sphere_chain_run(float ceil_half, f3 x0, f3 v0, int S, float e,
                                                         const float* __restrict__ xt, int64_t n, int64_t i, int steps,
