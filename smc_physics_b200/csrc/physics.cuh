@@ -945,6 +945,11 @@ __device__ __forceinline__ void sphere_solve_floor(float d, float restitution, f
 // THROUGH the call by value (position and the chain's loop state included): nothing of the caller is live across it,
 // so the calling convention gives the register allocator no reason to park the hot loop's values in local memory
 // (with v, w alone returned it spilled the position and the loop counters for every substep of every lane).
+#ifdef RS_NEAR_OUTLINE
+#define RS_NEAR_ATTR __noinline__
+#else
+#define RS_NEAR_ATTR __forceinline__
+#endif
 struct SphereChain {
   f3 x, v, w;
   float restitution, ceil_half;
@@ -1001,31 +1006,16 @@ __device__ __forceinline__ void face_solve(float s, float rhs_n, float& vn, floa
   wb -= k * ja;
 }
 
-// One 1/240 s substep of the sphere on the chain state (orientation not tracked: it never feeds back into the motion).
-// In line, on scalars: free flight, the floor, the face of ONE wall (its face region: the centre between the wall's
-// edges, outside its core), and floor + wall face when the solver would not iterate (sphere_contacts_inline's
-// screening: neither normal row pushes / one pushes and the other stays idle).  These are 80 % of the substeps spent
-// within reach of a box in a filter run and all of those away from the boxes; the rest - wall edges, a centre inside
-// a wall, two walls, the ceiling, pairs that iterate - takes the call, with the whole chain state passed through it.
-__device__ __forceinline__ void sphere_chain_substep(SphereChain& c) {
+// The near-box tiers of sphere_chain_substep, optionally out of line (-DRS_NEAR_OUTLINE): the substep loop then holds
+// free flight and the floor only.  Pose-derived values are recomputed here; velocities come after the forces.
+__device__ RS_NEAR_ATTR SphereChain sphere_near_box_tiers(SphereChain c) {
   const float reach = PH_H + PH_THR;
   const float crest = c.restitution * PH_STATIC_REST;
   const float ax = fabsf(c.x.x), ay = fabsf(c.x.y);
   const bool nearx = ax > 0.5f - reach, neary = ay > 0.5f - reach;
-  const bool nearc = c.x.z > c.zc;  // zc = 1.01 - ceil_half - reach, kept in the chain state
+  const bool nearc = c.x.z > c.zc;
   const float d = c.x.z - PH_H;
   {
-    // v += dt (g - k v (1 + |v|))  written as  v <- v (1 - dt k (1 + |v|)) + dt g: one multiplier per vector instead of
-    // a product and an FMA per component (7 instructions less per substep); the same number up to the last bit
-    const float a = 1.0f - PH_DT * PH_DAMP, b = -(PH_DT * PH_DAMP);
-    const float gv = fmaf(sqrtf(dot3(c.v, c.v)), b, a);
-    c.v = mk3(c.v.x * gv, c.v.y * gv, fmaf(c.v.z, gv, PH_DT * PH_G));
-    const float gw = fmaf(sqrtf(dot3(c.w, c.w)), b, a);
-    c.w = mk3(c.w.x * gw, c.w.y * gw, c.w.z * gw);
-  }
-  if (!(nearx || neary || nearc)) {
-    if (d < PH_THR) face_solve(1.0f, face_rhs(1.0f, d, crest, c.v.z), c.v.z, c.v.x, c.v.y, c.w.x, c.w.y);
-  } else {
     bool slow = true;
     const float aw = nearx ? ax : ay;  // distance of the centre from the arena centre across the wall
     // face region of exactly one wall: closest point of the wall's core box (half thickness 0.01 - margin, spanning
@@ -1078,6 +1068,36 @@ __device__ __forceinline__ void sphere_chain_substep(SphereChain& c) {
       }
     }
     if (slow) c = sphere_contacts_near_box(c);
+  }
+  return c;
+}
+
+// One 1/240 s substep of the sphere on the chain state (orientation not tracked: it never feeds back into the motion).
+// In line, on scalars: free flight, the floor, the face of ONE wall (its face region: the centre between the wall's
+// edges, outside its core), and floor + wall face when the solver would not iterate (sphere_contacts_inline's
+// screening: neither normal row pushes / one pushes and the other stays idle).  These are 80 % of the substeps spent
+// within reach of a box in a filter run and all of those away from the boxes; the rest - wall edges, a centre inside
+// a wall, two walls, the ceiling, pairs that iterate - takes the call, with the whole chain state passed through it.
+__device__ __forceinline__ void sphere_chain_substep(SphereChain& c) {
+  const float reach = PH_H + PH_THR;
+  const float crest = c.restitution * PH_STATIC_REST;
+  const float ax = fabsf(c.x.x), ay = fabsf(c.x.y);
+  const bool nearx = ax > 0.5f - reach, neary = ay > 0.5f - reach;
+  const bool nearc = c.x.z > c.zc;  // zc = 1.01 - ceil_half - reach, kept in the chain state
+  const float d = c.x.z - PH_H;
+  {
+    // v += dt (g - k v (1 + |v|))  written as  v <- v (1 - dt k (1 + |v|)) + dt g: one multiplier per vector instead of
+    // a product and an FMA per component (7 instructions less per substep); the same number up to the last bit
+    const float a = 1.0f - PH_DT * PH_DAMP, b = -(PH_DT * PH_DAMP);
+    const float gv = fmaf(sqrtf(dot3(c.v, c.v)), b, a);
+    c.v = mk3(c.v.x * gv, c.v.y * gv, fmaf(c.v.z, gv, PH_DT * PH_G));
+    const float gw = fmaf(sqrtf(dot3(c.w, c.w)), b, a);
+    c.w = mk3(c.w.x * gw, c.w.y * gw, c.w.z * gw);
+  }
+  if (!(nearx || neary || nearc)) {
+    if (d < PH_THR) face_solve(1.0f, face_rhs(1.0f, d, crest, c.v.z), c.v.z, c.v.x, c.v.y, c.w.x, c.w.y);
+  } else {
+    c = sphere_near_box_tiers(c);
   }
   c.x = c.x + c.v * PH_DT;
 }

@@ -482,6 +482,13 @@ __device__ __forceinline__ SphereChain sphere_chain_run(float ceil_half, f3 x0, 
 #ifdef RS_STEP_CLOCK
       const long long clk0 = clock64();
 #endif
+#ifdef RS_UNROLL5
+      if (c.S == 5) {
+        c.sub = 0;
+#pragma unroll
+        for (int u = 0; u < 5; u++) sphere_chain_substep(c);
+      } else
+#endif
 #pragma unroll 1
       for (c.sub = c.S; c.sub > 0; c.sub--) sphere_chain_substep(c);
 #ifdef RS_STEP_CLOCK

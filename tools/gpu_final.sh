@@ -22,12 +22,12 @@ timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 7000 -
     --log-file gpurun_out/launches_$R.csv $SHORT > gpurun_out/ncu_launches_$R.log 2>&1
 echo "launch list exit $?"
 timeout 600 $SHORT > gpurun_out/plain2_$R.log 2>&1 &&
-timeout 1500 ncu --set full --clock-control none --import-source on -k regex:k_rejuvenate -s 60 -c 1 \
+timeout 1500 ncu --set full --clock-control none --import-source on -k regex:k_rejuvenate -s 85 -c 1 \
     -f -o gpurun_out/rejuv_sphere_$R $SHORT > gpurun_out/ncu_full_sphere_$R.log 2>&1
 echo "sphere capture exit $?"
 SHORTC="$SHORT --shape cube --particles 262144"
 timeout 600 $SHORTC > gpurun_out/plain3_$R.log 2>&1 &&
-timeout 1500 ncu --set full --clock-control none --import-source on -k regex:k_rejuvenate -s 60 -c 1 \
+timeout 1500 ncu --set full --clock-control none --import-source on -k regex:k_rejuvenate -s 85 -c 1 \
     -f -o gpurun_out/rejuv_cube_$R $SHORTC > gpurun_out/ncu_full_cube_$R.log 2>&1
 echo "cube capture exit $?"
 ls gpurun_out | wc -l
