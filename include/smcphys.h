@@ -179,6 +179,17 @@ int smcphys_resample_systematic(int32_t device, const double* log_w, int64_t n, 
  * u_k of counter (k, t) and the ancestor min{ i : C_i > floor(u_k W / 2^64) } on the same integer CDF. */
 int smcphys_resample_multinomial(int32_t device, const double* log_w, int64_t n, uint64_t seed, int32_t t,
                                  int64_t* idx_out);
+/* Allocation-free variant of smcphys_resample_systematic.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops).  d_log_w and
+ * d_idx_out are DEVICE pointers on `device` (n doubles in, n int64 out); the work is enqueued on cuda_stream
+ * (cudaStream_t as void*, NULL = default stream) and NOT synchronised.  All scratch (integer CDF, ancestors, tile sums,
+ * control block: 12.6 MB) lives in one static device array of the library, so n <= SMCPHYS_NOALLOC_MAX_N (larger n is
+ * rejected with SMCPHYS_EINVAL), every GPU that loads the library holds the array until exit, and every call shares it:
+ * calls that overlap on one GPU race - order them on one stream.  Calls no cudaMalloc / cudaFree / allocating routine.
+ * Same indices as smcphys_resample_systematic, bit for bit. */
+#define SMCPHYS_NOALLOC_MAX_N (1 << 20)
+int smcphys_resample_systematic_noalloc(int32_t device, const double* d_log_w, int64_t n, double u0, int64_t* d_idx_out,
+                                        void* cuda_stream);
 /* out3 = {max, ESS, LSE}; sums3 = {W, S1, S2} */
 int smcphys_weight_stats(int32_t device, const double* log_w, int64_t n, double* out3, uint64_t* sums3);
 

@@ -78,6 +78,7 @@ SIGNATURES = {
                                    C.c_int64, C.c_int32, _fp, _dp, _fp]),
     "smcphys_resample_systematic": (C.c_int, [C.c_int32, _dp, C.c_int64, C.c_double, _ip]),
     "smcphys_resample_multinomial": (C.c_int, [C.c_int32, _dp, C.c_int64, C.c_uint64, C.c_int32, _ip]),
+    "smcphys_resample_systematic_noalloc": (C.c_int, [C.c_int32, C.c_void_p, C.c_int64, C.c_double, C.c_void_p, C.c_void_p]),
     "smcphys_weight_stats": (C.c_int, [C.c_int32, _dp, C.c_int64, _dp, _up]),
     "smcphys_set_profiling": (C.c_int, [_H, C.c_int32]),
     "smcphys_kernel_time": (C.c_int, [_H, C.c_int32, _dp, _ip]),

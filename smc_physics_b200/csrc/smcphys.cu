@@ -2045,4 +2045,79 @@ int smcphys_resample_multinomial(int32_t device, const double* log_w, int64_t n,
   return 0;
 }
 
+
+// ---------------------------------------------------------------- allocation-free entry
+// smcphys_resample_systematic on DEVICE buffers with every byte of scratch in a file-scope device array: nothing here
+// calls cudaMalloc / cudaFree or any allocating routine, so it can be used where those are forbidden (CUDA graph
+// capture, tight serving loops).  Scratch layout (256-byte aligned pieces): integer CDF u64[MAX_N], ancestors
+// i32[MAX_N], tile sums / offsets u64[MAX_N / 1024] each, control block.  Every GPU that loads the library holds the
+// array until exit; every call shares it, so calls that overlap on one GPU race.
+#define NA_MAX_N SMCPHYS_NOALLOC_MAX_N
+#define NA_TILES ((NA_MAX_N + TILE - 1) / TILE)
+#define NA_ALIGN(x) (((x) + 255) & ~(size_t)255)
+#define NA_OFF_CDF ((size_t)0)
+#define NA_OFF_IDX (NA_OFF_CDF + NA_ALIGN(sizeof(u64) * (size_t)NA_MAX_N))
+#define NA_OFF_TSUM (NA_OFF_IDX + NA_ALIGN(sizeof(int) * (size_t)NA_MAX_N))
+#define NA_OFF_TOFF (NA_OFF_TSUM + NA_ALIGN(sizeof(u64) * (size_t)NA_TILES))
+#define NA_OFF_CTL (NA_OFF_TOFF + NA_ALIGN(sizeof(u64) * (size_t)NA_TILES))
+#define NA_BYTES (NA_OFF_CTL + NA_ALIGN(sizeof(Ctl)))
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NA_BYTES];
+
+}  // extern "C"
+#include <mutex>
+// In host code `g_noalloc_scratch` is a host-side stand-in, not a device address: the address a kernel may use comes
+// from cudaGetSymbolAddress, taken once per device with that device current.
+static std::mutex g_noalloc_mu;
+static unsigned char* g_noalloc_ptr[SMCPHYS_MAX_RANKS] = {nullptr};
+static int noalloc_scratch(int device, unsigned char** out) {
+  if (device < 0 || device >= SMCPHYS_MAX_RANKS) return fail(SMCPHYS_EINVAL, "device ordinal out of range");
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    void* p = nullptr;
+    CK(cudaGetSymbolAddress(&p, g_noalloc_scratch));  // the caller has made `device` current
+    g_noalloc_ptr[device] = (unsigned char*)p;
+  }
+  *out = g_noalloc_ptr[device];
+  return 0;
+}
+extern "C" {
+
+int smcphys_resample_systematic_noalloc(int32_t device, const double* d_log_w, int64_t n, double u0, int64_t* d_idx_out,
+                                        void* cuda_stream) {
+  if (n < 0) return fail(SMCPHYS_EINVAL, "n must be >= 0");
+  if (n > (int64_t)NA_MAX_N)
+    return fail(SMCPHYS_EINVAL, "resample_systematic_noalloc: n = " + std::to_string(n) + " exceeds SMCPHYS_NOALLOC_MAX_N = " +
+                                    std::to_string((long long)NA_MAX_N) + " (the static scratch array); use "
+                                    "smcphys_resample_systematic for larger inputs");
+  if (n == 0) return 0;
+  if (!d_log_w || !d_idx_out) return fail(SMCPHYS_EINVAL, "NULL argument");
+  if (!(u0 >= 0.0 && u0 < 1.0)) return fail(SMCPHYS_EINVAL, "u0 must be in [0, 1)");
+  int rc = use_device(device);
+  if (rc) return rc;
+  unsigned char* base = nullptr;
+  rc = noalloc_scratch(device, &base);
+  if (rc) return rc;
+  cudaStream_t st = (cudaStream_t)cuda_stream;
+  Bufs B;
+  memset(&B, 0, sizeof(B));
+  B.logw = const_cast<double*>(d_log_w);  // read only by the kernels below
+  B.cdf = (u64*)(base + NA_OFF_CDF);
+  B.idx = (int*)(base + NA_OFF_IDX);
+  B.tile_sum = (u64*)(base + NA_OFF_TSUM);
+  B.tile_off = (u64*)(base + NA_OFF_TOFF);
+  Ctl* ctl = (Ctl*)(base + NA_OFF_CTL);
+  const int ntiles = (int)((n + TILE - 1) / TILE);
+  // the array keeps the last call's contents: the control block (running max, integer sums, block counter) must start
+  // at zero; CDF, indices and tile sums are fully rewritten for [0, n)
+  CK(cudaMemsetAsync(ctl, 0, sizeof(Ctl), st));
+  LAUNCH(k_block_max, nblk(n, 256), 256, st, B.logw, n, ctl);
+  LAUNCH(k_publish_max, 1, 1, st, ctl, (double*)nullptr);
+  LAUNCH(k_weight_sums, ntiles, TILE_THREADS, st, B, ctl, &ctl->gmax, n, ntiles, 0, (int64_t)1, (int64_t)2, 0,
+         (double*)nullptr, (double*)nullptr, (int*)nullptr, (u64*)nullptr);
+  LAUNCH(k_cdf, ntiles, TILE_THREADS, st, B, ctl, &ctl->gmax, n, (u64)0, 0, (const u64*)nullptr);
+  LAUNCH(k_index, nblk(n, 256), 256, st, B, ctl, n, n, (u64)(u0 * 4294967296.0), &ctl->W, (u64)0, (int64_t)0, n, 0);
+  LAUNCH(k_idx_to_i64, nblk(n, 256), 256, st, B.idx, d_idx_out, n);
+  return 0;
+}
+
 }  // extern "C"
