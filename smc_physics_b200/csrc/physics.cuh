@@ -637,7 +637,7 @@ __device__ __forceinline__ bool sphere_contacts_inline(SphereHit& hit, float res
 struct Body;
 __device__ __forceinline__ void apply_forces(Body& s);
 __device__ __forceinline__ void integrate_q(Body& s);
-// ---------------------------------------------------------------- sphere: multi-contact solve, block cooperative
+// ---------------------------------------------------------------- sphere: multi-contact solve (per thread, out of line)
 // Contacts of the sphere in the order the oracle / Bullet visits them: plane, then the boxes in creation order
 // (-x, +y, +x, -y, ceiling).  Only (n, dist) are kept; the arm is always -h n.
 __device__ __forceinline__ int sphere_contacts_ordered(const ScenePar& sp, const f3& x, f3* n, float* dist) {
@@ -1102,6 +1102,24 @@ __device__ __forceinline__ void sphere_chain_substep(SphereChain& c) {
   c.x = c.x + c.v * PH_DT;
 }
 
+// true when at least one normal row of the contact set has a positive right-hand side (see substep)
+__device__ __forceinline__ bool contacts_push(const Contact* c, int nc, float crest, const f3& v, const f3& w) {
+  bool push = false;
+#pragma unroll 1
+  for (int i = 0; i < nc; i++) {
+    const f3 n = c[i].n, r = c[i].r;
+    const float relv = dot3(n, v) + dot3(cross3(r, n), w);
+    float rest = 0.f;
+    if (fabsf(relv) >= PH_REST_THRESH) rest = fmaxf(0.f, -crest * relv);
+    const float distance = c[i].dist + PH_SLOP;
+    float verr = rest - relv, perr = 0.f;
+    if (distance > 0.f) verr -= distance / PH_DT;
+    else perr = -distance * PH_ERP / PH_DT;
+    push = push || (perr + verr > 0.f);
+  }
+  return push;
+}
+
 template <int SHAPE, bool TRACK_Q>
 __device__ __forceinline__ void substep(const ScenePar& sp, float restitution, Body& s, Manifold& pm) {
   const float dt = PH_DT;
@@ -1129,6 +1147,14 @@ __device__ __forceinline__ void substep(const ScenePar& sp, float restitution, B
     else pm.n = 0;
     const int npl = pm.n;  // the plane-manifold points come first in c[]
     apply_forces(s);
+#ifndef PH_NO_PUSH_SCREEN
+    // No normal row pushes (every contact is within the breaking threshold but separating, or hovering inside the
+    // margin): sweep 1 of the solver clamps every normal impulse to 0, every friction cone is then empty, the residual
+    // is 0 and it returns the velocities unchanged - exactly, for any contact set.  Checked here on the normal rows
+    // alone (10 instructions per contact instead of the ~60 of a row set-up + sweep); this is most of the contact
+    // substeps of a cube at rest (the cold manifold of every macro step re-collects its points one per substep).
+    if (nc > 0 && !contacts_push(c, nc, restitution * PH_STATIC_REST, s.v, s.w)) nc = 0;
+#endif
     if (nc > 0) {
 #ifdef PH_PLANE_ROLLED
       const VelPair r = (nc == npl) ? solve_plane_contacts(c, nc, restitution, s.v, s.w)
