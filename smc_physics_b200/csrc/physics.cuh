@@ -406,7 +406,7 @@ __device__ __noinline__ VelPair solve_plane_contacts(const Contact* c, int nc, f
 // top stall of the cube kernel and this loop half of its instructions (profiles/r02_cube_*).  Results are bit
 // identical to solve_plane_contacts.  One instantiation per contact count, dispatched by a switch: a single unrolled
 // body with every slot guarded by i < nc (so that lanes with different counts share instructions) was measured and is
-// slower, 11.64 M against 12.05 M particle-steps/s - the lanes of a warp are few in here (5.9 of 32) because most
+// slower (lineage-controlled A/B of the t = 119 launch: 40-41.5 ms against 38.5 ms) - the lanes of a warp are few in here (5.9 of 32) because most
 // contact sets are separating and leave after their first sweep, not because the counts differ.
 template <int NC>
 __device__ __forceinline__ VelPair solve_plane_reg(const Contact* c, float restitution, f3 v, f3 w) {
