@@ -7,7 +7,7 @@ timeout 900 python -m pytest tests -m gpu -x -q -s -k "nccl_ranks" > gpurun_out/
 while [ $# -ge 2 ]; do
   SH=$1; P=$2; shift; shift
   timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
-    bench.py --gpus $N --steps 2 --warmup 3 --shape $SH --particles $P > gpurun_out/bench_${N}gpu_${SH}_$R.json 2> gpurun_out/bench_${N}gpu_${SH}_$R.err
+    bench.py --gpus $N --steps ${STEPS:-2} --warmup 3 --shape $SH --particles $P > gpurun_out/bench_${N}gpu_${SH}_$R.json 2> gpurun_out/bench_${N}gpu_${SH}_$R.err
   echo "bench $N gpus $SH exit $?"; grep '^{' gpurun_out/bench_${N}gpu_${SH}_$R.json | python -c "
 import sys, json
 for l in sys.stdin:
