@@ -14,6 +14,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -983,13 +984,55 @@ struct ProfScope {
 
 static inline unsigned int nblk(int64_t n, int b) { return (unsigned int)((n + b - 1) / b); }
 
-struct DevScratch {  // device scratch that frees on scope exit (also on the early returns of CK / LAUNCH)
-  std::vector<void*> p;
-  ~DevScratch() { for (void* q : p) cudaFree(q); }
+// Device scratch of the getters and the stateless entries.  Pieces are carved from ONE grow-only pool per device, so a
+// host loop over PhySMC.forward_step (smcphys_sim_step per step) or over the getters does not pay cudaMalloc / cudaFree
+// per call: the first call that needs more than the pool holds takes separate blocks (freed on scope exit) and leaves
+// the pool grown for the next one.  A scope holds the device's pool mutex from its first get() to its end - every
+// user synchronises its stream before it returns, so the pool is idle when the next scope takes it.  Nothing leaks on
+// the early returns of CK / LAUNCH.
+struct DevPool {
+  std::mutex mu;
+  unsigned char* base = nullptr;
+  size_t cap = 0;
+};
+static DevPool g_pool[SMCPHYS_MAX_RANKS];
+struct DevScratch {
+  DevPool* pool = nullptr;
+  std::unique_lock<std::mutex> lk;
+  size_t used = 0, need = 0;
+  std::vector<void*> extra;
+  ~DevScratch() {
+    for (void* q : extra) cudaFree(q);
+    if (pool && need > pool->cap) {  // grow for the next call (with headroom); the pool is idle here
+      if (pool->base) cudaFree(pool->base);
+      pool->base = nullptr;
+      pool->cap = 0;
+      void* q = nullptr;
+      const size_t want = need + need / 4 + 4096;
+      if (cudaMalloc(&q, want) == cudaSuccess) { pool->base = (unsigned char*)q; pool->cap = want; }
+      else cudaGetLastError();
+    }
+  }
   template <class T> cudaError_t get(T** out, size_t count) {
+    if (!pool) {
+      int dev = 0;
+      cudaError_t e = cudaGetDevice(&dev);
+      if (e != cudaSuccess) return e;
+      if (dev >= 0 && dev < SMCPHYS_MAX_RANKS) {
+        pool = &g_pool[dev];
+        lk = std::unique_lock<std::mutex>(pool->mu);
+      }
+    }
+    const size_t bytes = ((count * sizeof(T) + 16) + 255) & ~(size_t)255;
+    need += bytes;
+    if (pool && used + bytes <= pool->cap) {
+      *out = (T*)(pool->base + used);
+      used += bytes;
+      return cudaSuccess;
+    }
     void* q = nullptr;
-    cudaError_t e = cudaMalloc(&q, count * sizeof(T) + 16);
-    if (e == cudaSuccess) p.push_back(q);
+    cudaError_t e = cudaMalloc(&q, bytes);
+    if (e == cudaSuccess) extra.push_back(q);
     *out = (T*)q;
     return e;
   }
