@@ -124,11 +124,16 @@ def cpu_leg(args, shape_id, trial, steps, warmup, threads=0):
 
 
 def kernel_source_hash():
-    """sha256 (first 16 hex) of the kernel sources: stamps ncu-derived numbers so that a stale capture is not reported."""
+    """sha256 (first 16 hex) of the DEVICE code: physics.cuh, rng.cuh and the kernel part of smcphys.cu (everything above
+    the handle section; #include lines left out).  Stamps ncu-derived numbers so that a capture of other kernels is not
+    reported, while host-side changes (entry points, scratch management) leave the stamp valid."""
     import hashlib
     h = hashlib.sha256()
-    for f in ("physics.cuh", "rng.cuh", "smcphys.cu"):
-        h.update(open(os.path.join(ROOT, "smc_physics_b200", "csrc", f), "rb").read())
+    d = os.path.join(ROOT, "smc_physics_b200", "csrc")
+    for f in ("physics.cuh", "rng.cuh"):
+        h.update(open(os.path.join(d, f), "rb").read())
+    kern = open(os.path.join(d, "smcphys.cu")).read().split("// ---------------------------------------------------------------- handle")[0]
+    h.update("\n".join(l for l in kern.split("\n") if not l.startswith("#include")).encode())
     return h.hexdigest()[:16]
 
 
