@@ -1464,13 +1464,14 @@ static int copy_stats(smcphys_handle* h, int32_t R, smcphys_step_stats* per_step
 
 int smcphys_run_smc(smcphys_handle* h, int32_t R, smcphys_step_stats* per_step) {
   if (!h) return fail(SMCPHYS_EINVAL, "NULL handle");
+  if (h->kids.size() == 1) return smcphys_run_smc(h->kids[0], R, per_step);  // a group of one shard is an ordinary filter
   if (!h->kids.empty() || h->cfg.global_particles != h->cfg.num_particles) {
     std::vector<smcphys_handle*> S;
     if (!h->kids.empty()) S = h->kids;
     else S.push_back(h);
     for (auto* s : S) {
       if (!s->trial_set) return fail(SMCPHYS_ESTATE, "no trial: call smcphys_set_trial first");
-      if (!s->comm && s->nranks != (int)S.size())
+      if (!s->comm && (!s->parent || s->nranks != (int)S.size()))
         return fail(SMCPHYS_ESTATE, "sharded handle without a communicator: call smcphys_comm_init_rank (one process "
                                     "per GPU) or use smcphys_create_multi, or drive the smcphys_pf_* phases yourself");
       if (s->cfg.resampler != SMCPHYS_RESAMPLE_SYSTEMATIC)

@@ -355,6 +355,32 @@ def test_device_sharded_group_bit_identical_to_single_shard(sp, shape, G, n):
     assert abs(ml1 - ml2) < 1e-9 * (1 + abs(ml1))
 
 
+def test_group_edge_cases(sp):
+    """a group of ONE shard is an ordinary filter; a sharded handle without communicator refuses to run; empty trial"""
+    T = 10
+    path = _truth_path(0, 0.6, T)
+    with sp.ParticleFilter(num_particles=300, shape=0, substeps=5, max_timesteps=T, seed=5) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        pf.run_smc(R=1, want_stats=False)
+        one = pf.get_particles()
+    with sp.ParticleFilter(devices=[0], num_particles=300, shape=0, substeps=5, max_timesteps=T, seed=5) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        st = pf.run_smc(R=1)
+        g1 = pf.get_particles()
+        assert len(st) == T
+    assert np.array_equal(one["e"], g1["e"]) and np.array_equal(one["score"], g1["score"])
+    with sp.ParticleFilter(num_particles=100, global_particles=200, particle_offset=100, max_timesteps=T) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        with pytest.raises(sp.SmcphysError) as ei:
+            pf.run_smc()
+        assert ei.value.code == -3 and "communicator" in str(ei.value)
+    with sp.ParticleFilter(devices=[0, 0], num_particles=64, max_timesteps=T) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, np.zeros((0, 3)))          # no observations: the prior, on both shards
+        pf.run_smc()
+        e = pf.get_particles(want_score=False)["e"]
+        assert e.shape == (128,) and e.min() > 0 and e.max() < 1 and np.unique(e).size > 120
+
+
 def test_log_ml_on_device_matches_oracle(sp):
     T = 12
     path = _truth_path(0, 0.6, T)
