@@ -124,15 +124,16 @@ def cpu_leg(args, shape_id, trial, steps, warmup, threads=0):
 
 
 def kernel_source_hash():
-    """sha256 (first 16 hex) of the DEVICE code: physics.cuh, rng.cuh and the kernel part of smcphys.cu (everything above
-    the handle section; #include lines left out).  Stamps ncu-derived numbers so that a capture of other kernels is not
-    reported, while host-side changes (entry points, scratch management) leave the stamp valid."""
+    """sha256 (first 16 hex) of the code k_rejuvenate is compiled from: physics.cuh, rng.cuh and smcphys.cu up to the end
+    of k_rejuvenate (the section marker that follows it; #include lines left out).  Stamps ncu-derived numbers so that a
+    capture of another kernel body is not reported, while changes elsewhere (entry points, scratch management, the
+    kernels of the sharded exchange) leave the stamp valid."""
     import hashlib
     h = hashlib.sha256()
     d = os.path.join(ROOT, "smc_physics_b200", "csrc")
     for f in ("physics.cuh", "rng.cuh"):
         h.update(open(os.path.join(d, f), "rb").read())
-    kern = open(os.path.join(d, "smcphys.cu")).read().split("// ---------------------------------------------------------------- handle")[0]
+    kern = open(os.path.join(d, "smcphys.cu")).read().split("// ---------------------------------------------------------------- getters / stateless kernels")[0]
     h.update("\n".join(l for l in kern.split("\n") if not l.startswith("#include")).encode())
     return h.hexdigest()[:16]
 

@@ -101,7 +101,8 @@ int smcphys_predict(smcphys_handle* h, int32_t n_steps, float* pos_out, float* o
  * the same set_trial / run_smc / get_particles calls, the particles of a trial are sharded over the GPUs).
  * Per PF step, all stream ordered with no host synchronisation: local max -> all-reduce(max) -> integer weight sums
  * -> all-gather -> ESS decision, CDF offset and offspring slot range on the device -> ancestors -> the offspring are
- * STORED into the destination rank's idle buffers through peer memory (NVLink) -> barrier -> rejuvenation.
+ * STORED into the destination rank's idle buffers through peer memory (NVLink) -> barrier -> rejuvenation.  (Multinomial
+ * resampler: barrier -> every rank draws the parents of its own slots, searches the owning rank's CDF and PULLS them.)
  *
  * (a) One process per GPU (torchrun, MPI, Julia Distributed workers): every rank creates its handle with
  *     num_particles = N / nranks, global_particles = N, particle_offset = rank * num_particles, rank 0 calls

@@ -886,6 +886,67 @@ __global__ void __launch_bounds__(256) k_push_hist(Bufs B, const Ctl* ctl, const
       if (c0 + c < c1) dst[(int64_t)c * n] = v[c];
   }
 }
+// ---- multinomial parents on a sharded filter.  The parents are i.i.d., not sorted, so there is no offspring range to
+// push: every rank draws the thresholds of ITS OWN slots (Philox counter = global slot, as on one shard), finds the
+// rank whose integer weight interval holds the threshold, searches that rank's CDF through peer memory and PULLS the
+// ancestor's payload into its idle buffers.  CDFs hold global values (own prefix sum + W_before), so the ancestors are
+// the single-shard ones, bit for bit.  `all` = NCCL all-gather of the sums, or NULL: read the peers' sums directly.
+__global__ void k_index_multi_sh(Bufs B, const Ctl* ctl, const u64* all, const Peer* __restrict__ peers, int G,
+                                 int64_t n, int64_t goff, u64 seed, int t) {
+  if (!ctl->resampled) return;
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  uint32_t r[4];
+  philox4x32_10(seed, (uint32_t)(goff + j), (uint32_t)t, 0u, (uint32_t)ST_RESAMPLE_MULTI, r);
+  const u64 u = ((u64)r[0] << 32) | (u64)r[1];
+  const u64 tau = multi_threshold(u, ctl->W_total);
+  int owner = G - 1;
+  u64 before = 0;
+  for (int q = 0; q < G; q++) {
+    const u64 w = all ? all[3 * q] : ((const volatile u64*)peers[q].sums)[0];
+    if (tau < before + w) { owner = q; break; }
+    before += w;
+  }
+  const u64* __restrict__ cdf = peers[owner].cdf;
+  int64_t lo = 0, hi = n - 1;
+  while (lo < hi) {
+    int64_t mid = (lo + hi) >> 1;
+    if (cdf[mid] > tau) hi = mid; else lo = mid + 1;
+  }
+  B.idx[j] = (int)lo;
+  B.idx[n + j] = owner;  // the ancestor scratch of a sharded filter holds N >= 2 n entries
+}
+__global__ void k_pull(Bufs B, const Ctl* ctl, const Peer* __restrict__ peers, int64_t n) {
+  if (!ctl->resampled) return;
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const int cur = ctl->cur, nxt = cur ^ 1;  // every rank holds the same `cur`: identical decisions
+  const int64_t a = B.idx[j];
+  const Peer P = peers[B.idx[n + j]];
+  B.e[nxt][j] = P.e[cur][a];
+  B.qs[nxt][j] = P.qs[cur][a];
+#pragma unroll
+  for (int c = 0; c < 13; c++) B.st[nxt][c * n + j] = P.st[cur][c * n + a];
+}
+__global__ void __launch_bounds__(256) k_pull_hist(Bufs B, const Ctl* ctl, const Peer* __restrict__ peers, int64_t n,
+                                                   int rows) {
+  if (!ctl->resampled) return;
+  const int64_t j = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= n) return;
+  const int cur = ctl->cur, nxt = cur ^ 1;
+  const int64_t a = B.idx[j];
+  const int c0 = (int)blockIdx.y * (GH_ROWS * 3), c1 = rows * 3;
+  const float* __restrict__ src = peers[B.idx[n + j]].xt[cur] + (int64_t)c0 * n + a;
+  float* __restrict__ dst = B.xt[nxt] + (int64_t)c0 * n + j;
+  float v[GH_ROWS * 3];
+#pragma unroll
+  for (int c = 0; c < GH_ROWS * 3; c++)
+    if (c0 + c < c1) v[c] = src[(int64_t)c * n];
+#pragma unroll
+  for (int c = 0; c < GH_ROWS * 3; c++)
+    if (c0 + c < c1) __stcs(dst + (int64_t)c * n, v[c]);
+}
+
 // after the exchange: log weights := 0 (Gen.maybe_resample!).  Runs after the barrier that follows the pushes; the
 // log weights are single buffered and a rank's CDF is built from them, so nobody may reset them earlier.
 __global__ void k_post_resample(Bufs B, const Ctl* ctl, int64_t n) {
@@ -1404,24 +1465,56 @@ static int sharded_step(std::vector<smcphys_handle*>& S, int t, int R) {
   }
   uint32_t r[4];
   philox4x32_10(S[0]->cfg.seed, 0u, (uint32_t)t, 0u, (uint32_t)ST_RESAMPLE, r);
-  // decision, CDF, ancestors, and the offspring stored into their destination shard
+  const bool multinomial = S[0]->cfg.resampler == SMCPHYS_RESAMPLE_MULTINOMIAL;
+  // decision and the shard's CDF (global values: own prefix sums + the weight of all lower ranks)
   for (auto* s : S) {
     CK(cudaSetDevice(s->cfg.device));
     const int64_t n = s->cfg.num_particles, N = s->cfg.global_particles;
-    {
-      ProfScope ps(s, SMCPHYS_K_WEIGHTS);
-      LAUNCH(k_decide, 1, 1, s->stream, s->ctl, use_nccl ? (const u64*)s->d_all : (const u64*)nullptr, s->d_peers,
-             s->nranks, s->rank, N, s->cfg.ess_num, s->cfg.ess_den, (u64)r[0], t, s->d_ess, s->d_lse, s->d_res);
-      LAUNCH(k_cdf, s->ntiles, TILE_THREADS, s->stream, s->B, s->ctl, &s->ctl->gmax, n, (u64)0, 1,
-             (const u64*)&s->ctl->W_before);
-      LAUNCH(k_index_sh, nblk(n, 256), 256, s->stream, s->B, s->ctl, n, N);
-    }
-    ProfScope ps(s, SMCPHYS_K_GATHER);
-    LAUNCH(k_push, nblk(n, 256), 256, s->stream, s->B, s->ctl, s->d_peers, n);
-    LAUNCH(k_push_hist, dim3(nblk(n, 256), (unsigned)((t + GH_ROWS) / GH_ROWS)), 256, s->stream, s->B, s->ctl, s->d_peers,
-           n, t + 1);
+    ProfScope ps(s, SMCPHYS_K_WEIGHTS);
+    LAUNCH(k_decide, 1, 1, s->stream, s->ctl, use_nccl ? (const u64*)s->d_all : (const u64*)nullptr, s->d_peers,
+           s->nranks, s->rank, N, s->cfg.ess_num, s->cfg.ess_den, (u64)r[0], t, s->d_ess, s->d_lse, s->d_res);
+    LAUNCH(k_cdf, s->ntiles, TILE_THREADS, s->stream, s->B, s->ctl, &s->ctl->gmax, n, (u64)0, 1,
+           (const u64*)&s->ctl->W_before);
   }
-  // every shard's stores have landed before anyone reads its new buffer
+  if (!multinomial) {
+    // systematic: ancestors of this shard's offspring range, stored into their destination shard (push)
+    for (auto* s : S) {
+      CK(cudaSetDevice(s->cfg.device));
+      const int64_t n = s->cfg.num_particles, N = s->cfg.global_particles;
+      {
+        ProfScope ps(s, SMCPHYS_K_WEIGHTS);
+        LAUNCH(k_index_sh, nblk(n, 256), 256, s->stream, s->B, s->ctl, n, N);
+      }
+      ProfScope ps(s, SMCPHYS_K_GATHER);
+      LAUNCH(k_push, nblk(n, 256), 256, s->stream, s->B, s->ctl, s->d_peers, n);
+      LAUNCH(k_push_hist, dim3(nblk(n, 256), (unsigned)((t + GH_ROWS) / GH_ROWS)), 256, s->stream, s->B, s->ctl,
+             s->d_peers, n, t + 1);
+    }
+  } else {
+    // multinomial: every shard's CDF must be complete before anyone searches it ...
+    if (use_nccl) {
+      for (auto* s : S) NCCLCK(nccl().AllReduce(s->d_bar, s->d_bar, 1, ncclInt, ncclSum, s->comm, s->stream));
+    } else {
+      rc = group_sync(S);
+      if (rc) return rc;
+    }
+    // ... then each shard draws the parents of its own slots and pulls them through the peer table
+    for (auto* s : S) {
+      CK(cudaSetDevice(s->cfg.device));
+      const int64_t n = s->cfg.num_particles;
+      {
+        ProfScope ps(s, SMCPHYS_K_WEIGHTS);
+        LAUNCH(k_index_multi_sh, nblk(n, 256), 256, s->stream, s->B, s->ctl,
+               use_nccl ? (const u64*)s->d_all : (const u64*)nullptr, s->d_peers, s->nranks, n, s->cfg.particle_offset,
+               s->cfg.seed, t);
+      }
+      ProfScope ps(s, SMCPHYS_K_GATHER);
+      LAUNCH(k_pull, nblk(n, 256), 256, s->stream, s->B, s->ctl, s->d_peers, n);
+      LAUNCH(k_pull_hist, dim3(nblk(n, 256), (unsigned)((t + GH_ROWS) / GH_ROWS)), 256, s->stream, s->B, s->ctl,
+             s->d_peers, n, t + 1);
+    }
+  }
+  // every shard's stores / loads of this step have completed before anyone reads its new buffer or reuses the old one
   if (use_nccl) {
     for (auto* s : S) NCCLCK(nccl().AllReduce(s->d_bar, s->d_bar, 1, ncclInt, ncclSum, s->comm, s->stream));
   } else {
@@ -1474,8 +1567,6 @@ int smcphys_run_smc(smcphys_handle* h, int32_t R, smcphys_step_stats* per_step) 
       if (!s->comm && (!s->parent || s->nranks != (int)S.size()))
         return fail(SMCPHYS_ESTATE, "sharded handle without a communicator: call smcphys_comm_init_rank (one process "
                                     "per GPU) or use smcphys_create_multi, or drive the smcphys_pf_* phases yourself");
-      if (s->cfg.resampler != SMCPHYS_RESAMPLE_SYSTEMATIC)
-        return fail(SMCPHYS_ESTATE, "the sharded filter resamples systematically (order preserving offspring ranges)");
     }
     if (R < 0) R = S[0]->cfg.rejuvenation_moves;
     int rc = 0;

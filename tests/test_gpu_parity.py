@@ -355,6 +355,36 @@ def test_device_sharded_group_bit_identical_to_single_shard(sp, shape, G, n):
     assert abs(ml1 - ml2) < 1e-9 * (1 + abs(ml1))
 
 
+@pytest.mark.parametrize("shape,G,n", [(0, 2, 500), (0, 3, 333), (1, 4, 128)])
+def test_device_sharded_multinomial_bit_identical_to_single_shard(sp, shape, G, n):
+    """Multinomial parents (Gen.maybe_resample!) on a sharded filter: parents are not sorted, so every shard draws the
+    parents of its own slots and PULLS them through the peer table.  Same particles as the unsharded multinomial filter."""
+    T, R = 20, 2
+    path = _truth_path(shape, 0.6, T)
+    with sp.ParticleFilter(num_particles=G * n, shape=shape, substeps=5, max_timesteps=T, seed=33,
+                           resampler=sp.MULTINOMIAL) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        stats = pf.run_smc(R=R)
+        one = pf.get_particles(want_traj=True)
+        ml1 = pf.get_log_ml()
+    with sp.ParticleFilter(devices=[0] * G, num_particles=n, shape=shape, substeps=5, max_timesteps=T, seed=33,
+                           resampler=sp.MULTINOMIAL) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        st2 = pf.run_smc(R=R)
+        many = pf.get_particles(want_traj=True)
+        ml2 = pf.get_log_ml()
+    assert sum(s["resampled"] for s in stats) >= 2
+    assert [s["resampled"] for s in stats] == [s["resampled"] for s in st2]
+    for k in ("e", "log_w", "score", "traj"):
+        assert np.array_equal(one[k], many[k]), k
+    assert abs(ml1 - ml2) < 1e-9 * (1 + abs(ml1))
+    # and it is not the systematic filter
+    with sp.ParticleFilter(num_particles=G * n, shape=shape, substeps=5, max_timesteps=T, seed=33) as pf:
+        pf.set_trial(INIT_POS, INIT_VEL, path)
+        pf.run_smc(R=R, want_stats=False)
+        assert not np.array_equal(pf.get_particles(want_score=False)["e"], one["e"])
+
+
 def test_group_edge_cases(sp):
     """a group of ONE shard is an ordinary filter; a sharded handle without communicator refuses to run; empty trial"""
     T = 10
@@ -392,7 +422,7 @@ def test_log_ml_on_device_matches_oracle(sp):
     assert abs(ml - ref["log_ml"]) < 1e-6 * (1 + abs(ref["log_ml"]))
 
 
-def _nccl_worker(rank, world, port, shape, n, T, R, q):
+def _nccl_worker(rank, world, port, shape, n, T, R, q, resampler=0):
     import os
     import sys
     import torch
@@ -404,7 +434,7 @@ def _nccl_worker(rank, world, port, shape, n, T, R, q):
     try:
         from smc_physics_b200.sharded import ShardedFilter
         f = ShardedFilter(particles_per_rank=n, shape=shape, substeps=5, max_timesteps=T, rejuvenation_moves=R,
-                          device=rank, seed=21)
+                          device=rank, seed=21, resampler=resampler)
         f.set_trial(INIT_POS, INIT_VEL, _truth_path(shape, 0.6, T))
         stats = f.run_smc(R)
         out = f.get_particles(want_traj=True)
@@ -416,8 +446,8 @@ def _nccl_worker(rank, world, port, shape, n, T, R, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("shape,n", [(0, 1000), (1, 300)])
-def test_nccl_ranks_bit_identical_to_single_shard(sp, shape, n):
+@pytest.mark.parametrize("shape,n,resampler", [(0, 1000, 0), (1, 300, 0), (0, 700, 1)])
+def test_nccl_ranks_bit_identical_to_single_shard(sp, shape, n, resampler):
     """The path bench.py --gpus N runs: one process per GPU, smcphys_comm_init_rank (NCCL + CUDA IPC), collective
     smcphys_run_smc.  Needs >= 2 visible devices (skipped on the single-GPU box)."""
     import torch
@@ -429,14 +459,15 @@ def test_nccl_ranks_bit_identical_to_single_shard(sp, shape, n):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = 29600 + (os.getpid() % 2000)
-    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, shape, n, T, R, q)) for r in range(world)]
+    procs = [ctx.Process(target=_nccl_worker, args=(r, world, port, shape, n, T, R, q, resampler)) for r in range(world)]
     for p in procs:
         p.start()
     outs = sorted([q.get(timeout=300) for _ in procs], key=lambda o: o[0])
     for p in procs:
         p.join(timeout=120)
         assert p.exitcode == 0
-    with sp.ParticleFilter(num_particles=world * n, shape=shape, substeps=5, max_timesteps=T, seed=21) as pf:
+    with sp.ParticleFilter(num_particles=world * n, shape=shape, substeps=5, max_timesteps=T, seed=21,
+                           resampler=resampler) as pf:
         pf.set_trial(INIT_POS, INIT_VEL, _truth_path(shape, 0.6, T))
         stats = pf.run_smc(R=R)
         one = pf.get_particles(want_traj=True)
