@@ -206,7 +206,9 @@ __global__ void __launch_bounds__(PF_BLOCK) k_extend(Bufs B, Ctl* ctl, TrialPar 
     lw = B.logw[i] + (o2 - 3.0 * log(tp.sigma_obs) - 3.0 * SMC_HALF_LOG_2PI);
     B.logw[i] = lw;
     s.x = mk3(xf[0], xf[1], xf[2]);
-    macro_step<SHAPE, true>(sp, (float)B.e[cur][i], S, s);
+    // a sphere's orientation never feeds back into its motion and no reader uses the stored one (the state getter
+    // re-simulates with orientation tracking): not integrated here either
+    macro_step<SHAPE, SHAPE == SHAPE_CUBE>(sp, (float)B.e[cur][i], S, s);
     store_body(st, n, i, s);
   }
   lw = warp_max(lw);
@@ -574,11 +576,13 @@ __global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : RJ
     const double inv2s2 = 0.5 / (tp.sigma_tr * tp.sigma_tr);
     float* st = B.st[cur];
     const float* xt_cur = B.xt[cur];
+    TruncZ z_old = truncnorm_z(e_old, prop_sigma, 0.0, 1.0);  // normaliser of the current elasticity, renewed on accept
     for (int j = 0; j < R; j++) {
       uint32_t r[4];
       philox4x32_10(seed, (uint32_t)(goff + i), (uint32_t)t, (uint32_t)(move0 + j), (uint32_t)ST_PROPOSAL, r);
       double log_qratio;  // log q(e | e') - log q(e' | e)
-      const double e_new = truncnorm_propose(u01(r[0]), e_old, prop_sigma, 0.0, 1.0, &log_qratio);
+      TruncZ z_new;
+      const double e_new = truncnorm_propose_z(u01(r[0]), e_old, z_old, prop_sigma, 0.0, 1.0, &z_new, &log_qratio);
       const double log_u = log(u01(r[1]));
       const ChainOut o = resimulate_call<SHAPE>(sp.ceil_half, mk3(tp.x0[0], tp.x0[1], tp.x0[2]),
                                                 mk3(tp.v0[0], tp.v0[1], tp.v0[2]), S, (float)e_new, xt_cur, n, i, t + 1);
@@ -590,6 +594,7 @@ __global__ void __launch_bounds__(RJ_BLOCK, SHAPE == SHAPE_SPHERE ? RJ_MINB : RJ
         // accepted: the simulator state goes out right away, so nothing but (e, q) stays live across the moves
         e_old = e_new;
         q_old = q_new;
+        z_old = z_new;
         acc++;
         st[0 * n + i] = s.x.x; st[1 * n + i] = s.x.y; st[2 * n + i] = s.x.z;
         if (SHAPE == SHAPE_CUBE) {  // a sphere keeps its stored quaternion (see above)
